@@ -1,0 +1,128 @@
+"""``nn.Module`` drop-ins backed by the native kernels (``state_dict`` keys identical to torch's).
+
+Each module subclasses its torch counterpart, so parameter names/shapes — and therefore the
+``model.pth`` checkpoints of the reference (``notebooks/code/cifar10-distributed-native-cpu.py:196-199``,
+``inference.py:28-34``) — are unchanged.  ``forward`` dispatches on the input: CUDA tensors run the
+sm_100a kernels on bf16 channels-last activations, CPU tensors run the reference fp32 math.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn as nn
+
+from ..ops import functional as BF
+
+
+class Conv2d(nn.Conv2d):
+    """conv (+bias) with an optional fused ReLU epilogue."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, bias=True, relu=False):
+        super().__init__(in_channels, out_channels, kernel_size, stride=stride, padding=padding, bias=bias)
+        if self.stride[0] != self.stride[1] or self.padding[0] != self.padding[1]:
+            raise ValueError("b200ddp.nn.Conv2d supports symmetric stride/padding only")
+        self.fused_relu = relu
+
+    def forward(self, x):
+        if x.is_cuda:
+            x = BF.as_activation(x)
+        return BF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0], self.fused_relu)
+
+
+class Linear(nn.Linear):
+    """linear (+bias) with an optional fused ReLU; ``nhwc_from=(C,H,W)`` marks a layer that consumes a
+    flattened conv activation whose reference column order is (c,h,w)."""
+
+    def __init__(self, in_features, out_features, bias=True, relu=False, nhwc_from=None):
+        super().__init__(in_features, out_features, bias=bias)
+        self.fused_relu = relu
+        self.nhwc_from = tuple(nhwc_from) if nhwc_from is not None else None
+
+    def forward(self, x):
+        if not x.is_cuda:
+            if x.dim() > 2:
+                x = x.flatten(1)
+            return BF.linear(x, self.weight, self.bias, self.fused_relu)
+        nh = None
+        if x.dim() == 4:
+            n, cp, h, w = x.shape
+            if self.nhwc_from is not None:
+                c = self.nhwc_from[0]
+                nh = (c, h, w, cp)
+            x = BF.flatten_nhwc(BF.as_activation(x))
+        else:
+            x = BF.as_activation(x)
+            kp = BF.ceil8(x.shape[1])
+            if kp != x.shape[1]:
+                x = torch.nn.functional.pad(x, (0, kp - x.shape[1]))
+        return BF.linear(x, self.weight, self.bias, self.fused_relu, nh)
+
+
+# When set, BatchNorm2d does not launch one `num_batches_tracked += 1` kernel per layer per step; the
+# trainer adds the step count once before a checkpoint is written (`flush_bn_counters`).
+_DEFER_BN_COUNTER = [False]
+
+
+def defer_bn_counters(flag: bool = True) -> None:
+    _DEFER_BN_COUNTER[0] = bool(flag)
+
+
+def flush_bn_counters(model: nn.Module, steps: int) -> None:
+    if steps <= 0:
+        return
+    for m in model.modules():
+        if isinstance(m, nn.BatchNorm2d) and m.num_batches_tracked is not None:
+            m.num_batches_tracked.add_(steps)
+
+
+class BatchNorm2d(nn.BatchNorm2d):
+    """BN with fused ReLU and residual add: ``y = relu(bn(x) + residual)``."""
+
+    def __init__(self, num_features, eps=1e-5, momentum=0.1, relu=False):
+        super().__init__(num_features, eps=eps, momentum=momentum)
+        self.fused_relu = relu
+
+    def forward(self, x, residual: Optional[torch.Tensor] = None):
+        training = self.training or not self.track_running_stats
+        if x.is_cuda:
+            x = BF.as_activation(x)
+            if residual is not None:
+                residual = BF.as_activation(residual)
+            if (self.training and self.track_running_stats and self.num_batches_tracked is not None
+                    and not _DEFER_BN_COUNTER[0]):
+                self.num_batches_tracked.add_(1)
+        return BF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, training,
+                             self.momentum if self.momentum is not None else 0.1, self.eps, self.fused_relu, residual)
+
+
+class MaxPool2d(nn.Module):
+    def __init__(self, kernel_size, stride=None, padding=0):
+        super().__init__()
+        self.kernel_size, self.stride, self.padding = kernel_size, stride if stride is not None else kernel_size, padding
+
+    def forward(self, x):
+        if x.is_cuda:
+            x = BF.as_activation(x)
+        return BF.max_pool2d(x, self.kernel_size, self.stride, self.padding)
+
+
+class GlobalAvgPool(nn.Module):
+    def forward(self, x):
+        return BF.global_avg_pool(x)
+
+
+class ReLU(nn.Module):
+    def forward(self, x):
+        return BF.relu(x)
+
+
+class CrossEntropyLoss(nn.Module):
+    """Mean softmax cross-entropy (``nn.CrossEntropyLoss()`` of the reference, …native-cpu.py:143)."""
+
+    def __init__(self, num_classes: Optional[int] = None):
+        super().__init__()
+        self.num_classes = num_classes
+
+    def forward(self, logits, targets):
+        return BF.cross_entropy(logits, targets, self.num_classes)

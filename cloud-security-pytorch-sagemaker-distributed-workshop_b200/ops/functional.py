@@ -1,0 +1,384 @@
+"""Autograd functions over the native sm_100a kernels, with the plain-PyTorch CPU fallback.
+
+On CUDA tensors every function below runs this package's kernels (tcgen05 conv/linear, fused
+BN+ReLU(+add), pools, fused softmax-CE); there is no library (cuDNN/cuBLAS) path on the GPU.  On CPU
+tensors the same functions evaluate the reference semantics with torch ops in fp32 — that is the
+CPU/gloo fallback of BASELINE.json config 1 and the oracle the numerics tests compare against.
+
+Weight gradients of native layers are deposited *directly* into the flat gradient arena when the
+parameter carries a ``_b200_sink`` (set by ``DistributedDataParallel``): the wgrad kernel accumulates
+into the (optimizer-zeroed) slot and the reducer is notified, so there is no autograd AccumulateGrad
+kernel and no separate bucket copy.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import native as nv
+
+CL = torch.channels_last
+
+
+def ceil8(v: int) -> int:
+    return (v + 7) // 8 * 8
+
+
+def as_activation(x: torch.Tensor, channels: Optional[int] = None) -> torch.Tensor:
+    """NCHW (any float dtype) -> bf16 channels-last activation, channel-padded to a multiple of 8."""
+    if x.dim() == 4:
+        c = x.shape[1]
+        cp = ceil8(c) if channels is None else channels
+        if cp != c:
+            x = F.pad(x, (0, 0, 0, 0, 0, cp - c))
+        if x.dtype != torch.bfloat16:
+            x = x.to(torch.bfloat16)
+        return x.contiguous(memory_format=CL)
+    if x.dtype != torch.bfloat16:
+        x = x.to(torch.bfloat16)
+    return x.contiguous()
+
+
+# ------------------------------------------------------------------------------------------------
+# weights: bf16 kernel-layout views ("shadow"), padded when channel counts are not multiples of 8
+# ------------------------------------------------------------------------------------------------
+def conv_weight_shadow(weight: torch.Tensor, cin_pad: int, cout_pad: int) -> torch.Tensor:
+    """[K,C,R,S] fp32 parameter -> bf16 [Kp,R,S,Cp] contiguous (kernel layout)."""
+    K, C, R, S = weight.shape
+    sh = getattr(weight, "_b200_shadow", None)
+    if sh is not None and cin_pad == C and cout_pad == K:
+        return sh                                   # maintained by the fused optimizer, zero cost
+    w = weight.detach().permute(0, 2, 3, 1)
+    if cin_pad != C or cout_pad != K:
+        w = F.pad(w, (0, cin_pad - C, 0, 0, 0, 0, 0, cout_pad - K))
+    return w.to(torch.bfloat16).contiguous()
+
+
+def linear_weight_shadow(weight: torch.Tensor, in_pad: int, out_pad: int, nhwc_from=None) -> torch.Tensor:
+    N, K = weight.shape
+    sh = getattr(weight, "_b200_shadow", None)
+    if sh is not None and in_pad == K and out_pad == N and nhwc_from is None:
+        return sh
+    w = weight.detach()
+    if nhwc_from is not None:           # columns are (c,h,w)-ordered in the reference; ours arrive (h,w,cp)
+        c, h, ww, cp = nhwc_from
+        w = w.view(N, c, h, ww).permute(0, 2, 3, 1)
+        if cp != c:
+            w = F.pad(w, (0, cp - c))
+        w = w.reshape(N, h * ww * cp)
+    if w.shape[1] != in_pad or N != out_pad:
+        w = F.pad(w, (0, in_pad - w.shape[1], 0, out_pad - N))
+    return w.to(torch.bfloat16).contiguous()
+
+
+def _pad_vec(b: Optional[torch.Tensor], n: int) -> Optional[torch.Tensor]:
+    if b is None:
+        return None
+    b = b.detach().float()
+    return b if b.numel() == n else F.pad(b, (0, n - b.numel()))
+
+
+def _deposit(param: torch.Tensor, grad_native: Optional[torch.Tensor], producer):
+    """Route a parameter gradient: straight into the arena slot if the parameter has a sink, else
+    return it to autograd.  ``producer(dst)`` must ACCUMULATE the gradient into ``dst`` (fp32)."""
+    sink = getattr(param, "_b200_sink", None)
+    if sink is not None and grad_native is None:
+        producer(sink.flat)
+        sink.done()
+        return None
+    return grad_native
+
+
+# ------------------------------------------------------------------------------------------------
+# conv2d (+bias +ReLU)
+# ------------------------------------------------------------------------------------------------
+class _Conv2dFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, pad, relu):
+        K, C, R, S = weight.shape
+        Cp, Kp = x.shape[1], ceil8(K)
+        w = conv_weight_shadow(weight, Cp, Kp)
+        b = _pad_vec(bias, Kp)
+        y = nv.conv_fwd(x, w, b, stride, pad, relu)
+        ctx.save_for_backward(x, w, y if relu else None)
+        ctx.meta = (weight, bias, stride, pad, relu, K, C, R, S, Cp, Kp)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, y = ctx.saved_tensors
+        weight, bias, stride, pad, relu, K, C, R, S, Cp, Kp = ctx.meta
+        dy = nv.to_cl(dy)
+        if relu:
+            dy = nv.relu_bwd(dy, y)
+        dx = nv.conv_dgrad(dy, w, x.shape, stride, pad) if ctx.needs_input_grad[0] else None
+        dw = None
+        if weight.requires_grad:
+            exact = (Cp == C and Kp == K)
+            sink = getattr(weight, "_b200_sink", None)
+            if exact and sink is not None:
+                nv.conv_wgrad_(sink.flat.view(K, R, S, C), x, dy, stride, pad)
+                sink.done()
+            else:
+                tmp = torch.zeros((Kp, R, S, Cp), dtype=torch.float32, device=x.device)
+                nv.conv_wgrad_(tmp, x, dy, stride, pad)
+                dw = tmp[:K, :, :, :C].permute(0, 3, 1, 2)
+                if sink is not None:
+                    sink.flat.view(K, R, S, C).add_(tmp[:K, :, :, :C])
+                    sink.done()
+                    dw = None
+        db = None
+        if bias is not None and bias.requires_grad:
+            g = dy.float().sum(dim=(0, 2, 3))[:K]
+            bsink = getattr(bias, "_b200_sink", None)
+            if bsink is not None:
+                bsink.flat[:K].add_(g)
+                bsink.done()
+            else:
+                db = g
+        return dx, dw, db, None, None, None
+
+
+def conv2d(x, weight, bias=None, stride=1, padding=0, relu=False):
+    if not x.is_cuda:
+        y = F.conv2d(x, weight, bias, stride=stride, padding=padding)
+        return F.relu(y) if relu else y
+    return _Conv2dFn.apply(x, weight, bias, int(stride), int(padding), bool(relu))
+
+
+# ------------------------------------------------------------------------------------------------
+# linear (+bias +ReLU) — a 1x1 convolution on the same tensor-core kernel
+# ------------------------------------------------------------------------------------------------
+class _LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu, nhwc_from):
+        N, K = weight.shape
+        Kp, Np = x.shape[1], ceil8(N)
+        w = linear_weight_shadow(weight, Kp, Np, nhwc_from)
+        b = _pad_vec(bias, Np)
+        y = nv.linear_fwd(x, w, b, relu)
+        ctx.save_for_backward(x, w, y if relu else None)
+        ctx.meta = (weight, bias, relu, N, K, Kp, Np, nhwc_from)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, y = ctx.saved_tensors
+        weight, bias, relu, N, K, Kp, Np, nhwc_from = ctx.meta
+        dy = dy.contiguous()
+        if relu:
+            dy = nv.relu_bwd(dy, y)
+        dx = nv.linear_dgrad(dy, w) if ctx.needs_input_grad[0] else None
+        dw = None
+        if weight.requires_grad:
+            sink = getattr(weight, "_b200_sink", None)
+            exact = (Kp == K and Np == N and nhwc_from is None)
+            if exact and sink is not None:
+                nv.linear_wgrad_(sink.flat.view(N, K), x, dy)
+                sink.done()
+            else:
+                tmp = torch.zeros((Np, Kp), dtype=torch.float32, device=x.device)
+                nv.linear_wgrad_(tmp, x, dy)
+                g = tmp[:N]
+                if nhwc_from is not None:
+                    c, h, ww, cp = nhwc_from
+                    g = g.view(N, h, ww, cp)[..., :c].permute(0, 3, 1, 2).reshape(N, K)
+                else:
+                    g = g[:, :K]
+                if sink is not None:
+                    sink.flat.view(N, K).add_(g)
+                    sink.done()
+                else:
+                    dw = g
+        db = None
+        if bias is not None and bias.requires_grad:
+            g = dy.float().sum(dim=0)[:N]
+            bsink = getattr(bias, "_b200_sink", None)
+            if bsink is not None:
+                bsink.flat[:N].add_(g)
+                bsink.done()
+            else:
+                db = g
+        return dx, dw, db, None, None
+
+
+def linear(x, weight, bias=None, relu=False, nhwc_from=None):
+    if not x.is_cuda:
+        y = F.linear(x, weight, bias)
+        return F.relu(y) if relu else y
+    return _LinearFn.apply(x, weight, bias, bool(relu), nhwc_from)
+
+
+# ------------------------------------------------------------------------------------------------
+# batch norm (+residual add +ReLU)
+# ------------------------------------------------------------------------------------------------
+class _BatchNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu):
+        if training:
+            stat = nv.bn_stats(x, gamma.detach(), beta.detach(), eps, momentum, running_mean, running_var)
+        else:
+            stat = nv.bn_eval_prep(gamma.detach(), beta.detach(), running_mean, running_var, eps)
+        y = nv.bn_apply(x, residual, stat, relu)
+        ctx.save_for_backward(x, y if relu else None, stat)
+        ctx.meta = (gamma, beta, relu, residual is not None, training)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y, stat = ctx.saved_tensors
+        gamma, beta, relu, has_res, training = ctx.meta
+        if not training:
+            raise RuntimeError("b200ddp BatchNorm: backward through eval-mode statistics is not supported")
+        dy = nv.to_cl(dy) if dy.dim() == 4 else dy.contiguous()
+        gs, bs = getattr(gamma, "_b200_sink", None), getattr(beta, "_b200_sink", None)
+        C = gamma.numel()
+        if gs is not None and bs is not None:
+            # the arena is zeroed by the optimizer, so beta_accum=1 both overwrites and accumulates correctly
+            dx, dres, _ = nv.bn_bwd(dy, x, y, stat, relu, has_res, gs.flat[:C], bs.flat[:C], 1.0)
+            gs.done()
+            bs.done()
+            return dx, dres, None, None, None, None, None, None, None, None
+        dx, dres, sums = nv.bn_bwd(dy, x, y, stat, relu, has_res)
+        return dx, dres, sums[1].clone(), sums[0].clone(), None, None, None, None, None, None
+
+
+def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum=0.1, eps=1e-5, relu=False, residual=None):
+    if not x.is_cuda:
+        y = F.batch_norm(x, running_mean, running_var, gamma, beta, training, momentum, eps)
+        if residual is not None:
+            y = y + residual
+        return F.relu(y) if relu else y
+    return _BatchNormFn.apply(x, residual, gamma, beta, running_mean, running_var, bool(training), float(momentum),
+                              float(eps), bool(relu))
+
+
+# ------------------------------------------------------------------------------------------------
+# pools, relu, flatten
+# ------------------------------------------------------------------------------------------------
+class _MaxPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, stride, pad):
+        y, amax = nv.maxpool_fwd(x, k, stride, pad)
+        ctx.save_for_backward(amax)
+        ctx.meta = (tuple(x.shape), k, stride, pad)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (amax,) = ctx.saved_tensors
+        shape, k, stride, pad = ctx.meta
+        return nv.maxpool_bwd(nv.to_cl(dy), amax, shape, k, stride, pad), None, None, None
+
+
+def max_pool2d(x, kernel_size, stride=None, padding=0):
+    stride = kernel_size if stride is None else stride
+    if not x.is_cuda:
+        return F.max_pool2d(x, kernel_size, stride, padding)
+    return _MaxPoolFn.apply(x, int(kernel_size), int(stride), int(padding))
+
+
+class _GlobalAvgPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        ctx.shape = tuple(x.shape)
+        return nv.avgpool_fwd(x)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return nv.avgpool_bwd(dy.contiguous(), ctx.shape)
+
+
+def global_avg_pool(x):
+    """AdaptiveAvgPool2d(1) + flatten -> [N, C]."""
+    if not x.is_cuda:
+        return x.mean(dim=(2, 3))
+    return _GlobalAvgPoolFn.apply(x)
+
+
+class _ReluFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        y = torch.relu(x)
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return nv.relu_bwd(dy.contiguous(memory_format=CL) if dy.dim() == 4 else dy.contiguous(), y)
+
+
+def relu(x):
+    return F.relu(x) if not x.is_cuda or x.dtype != torch.bfloat16 else _ReluFn.apply(x)
+
+
+def flatten_nhwc(x):
+    """[N,C,H,W] channels-last activation -> [N, H*W*C] matrix without moving data."""
+    if not x.is_cuda:
+        return x.flatten(1)
+    n, c, h, w = x.shape
+    return x.permute(0, 2, 3, 1).reshape(n, h * w * c)
+
+
+# ------------------------------------------------------------------------------------------------
+# losses
+# ------------------------------------------------------------------------------------------------
+class _CrossEntropyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, targets, num_classes):
+        lg = logits if logits.shape[1] == num_classes else logits[:, :num_classes]
+        lg = lg.contiguous()
+        loss, dlogits = nv.softmax_xent(lg, targets, 1.0 / lg.shape[0], want_grad=True)
+        ctx.save_for_backward(dlogits)
+        ctx.meta = (logits.shape[1], num_classes)
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        (dl,) = ctx.saved_tensors
+        width, nc = ctx.meta
+        if not _unit_loss_grad[0]:
+            dl = dl * gout.to(dl.dtype)
+        if width != nc:
+            dl = F.pad(dl, (0, width - nc))
+        return dl, None, None
+
+
+_unit_loss_grad = [False]
+
+
+def assume_unit_loss_grad(flag: bool = True):
+    """Trainer hint: ``loss.backward()`` is called on the raw loss (grad 1.0), skip the scale kernel."""
+    _unit_loss_grad[0] = bool(flag)
+
+
+def cross_entropy(logits, targets, num_classes: Optional[int] = None):
+    """Mean softmax cross-entropy.  ``num_classes`` < logits width ignores padded logit columns."""
+    nc = logits.shape[1] if num_classes is None else num_classes
+    if not logits.is_cuda:
+        return F.cross_entropy(logits[:, :nc].float(), targets)
+    return _CrossEntropyFn.apply(logits, targets, nc)
+
+
+class _BCEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, targets):
+        lg = logits.contiguous()
+        loss, dl = nv.bce_logits(lg, targets.float().contiguous(), 1.0 / lg.numel(), want_grad=True)
+        ctx.save_for_backward(dl)
+        ctx.shape = logits.shape
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        (dl,) = ctx.saved_tensors
+        return (dl * gout.to(dl.dtype)).view(ctx.shape), None
+
+
+def bce_with_logits(logits, targets):
+    if not logits.is_cuda:
+        return F.binary_cross_entropy_with_logits(logits.float(), targets.float())
+    return _BCEFn.apply(logits, targets)

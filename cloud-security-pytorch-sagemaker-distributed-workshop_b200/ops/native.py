@@ -1,0 +1,301 @@
+"""Thin, allocation-explicit Python wrappers over the C ABI (one function per native entry point).
+
+Conventions: activations are ``torch.bfloat16`` tensors with logical shape ``[N,C,H,W]`` in
+``channels_last`` memory format (physical NHWC) or plain ``[M,K]`` matrices; all wrappers launch on the
+current CUDA stream and never synchronise, so everything here is CUDA-graph capturable.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import byref, c_float, c_int, c_size_t, c_void_p
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib as L
+
+CL = torch.channels_last
+
+
+class ConvGeom(ctypes.Structure):
+    _fields_ = [("N", c_int), ("H", c_int), ("W", c_int), ("C", c_int), ("K", c_int),
+                ("R", c_int), ("S", c_int), ("stride", c_int), ("pad", c_int)]
+
+
+# --------------------------------------------------------------------------------------------
+# per-device scratch (BN partials + ticket counters, softmax ticket) — zeroed once, self-resetting
+# --------------------------------------------------------------------------------------------
+_SCRATCH = {}
+SCRATCH_BYTES = 8 << 20
+
+
+def scratch(device: torch.device) -> torch.Tensor:
+    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    t = _SCRATCH.get(key)
+    if t is None:
+        t = torch.zeros(SCRATCH_BYTES, dtype=torch.uint8, device=device)
+        _SCRATCH[key] = t
+    return t
+
+
+def _cl_ok(x: torch.Tensor) -> bool:
+    return x.dim() == 4 and x.is_contiguous(memory_format=CL)
+
+
+def to_cl(x: torch.Tensor) -> torch.Tensor:
+    return x if _cl_ok(x) else x.contiguous(memory_format=CL)
+
+
+def empty_act(n: int, c: int, h: int, w: int, device) -> torch.Tensor:
+    return torch.empty((n, c, h, w), dtype=torch.bfloat16, device=device, memory_format=CL)
+
+
+# --------------------------------------------------------------------------------------------
+# tensor-core conv / linear
+# --------------------------------------------------------------------------------------------
+def _geom(N, H, W, C, K, R, S, stride, pad) -> ConvGeom:
+    return ConvGeom(N, H, W, C, K, R, S, stride, pad)
+
+
+def conv_out_hw(H, W, R, S, stride, pad) -> Tuple[int, int]:
+    return (H + 2 * pad - R) // stride + 1, (W + 2 * pad - S) // stride + 1
+
+
+def conv_fwd(x: torch.Tensor, w_krsc: torch.Tensor, bias: Optional[torch.Tensor], stride: int, pad: int,
+             relu: bool) -> torch.Tensor:
+    """x [N,C,H,W] cl bf16, w [K,R,S,C] bf16 contiguous -> y [N,K,Ho,Wo] cl bf16."""
+    N, C, H, W = x.shape
+    K, R, S, C2 = w_krsc.shape
+    assert C2 == C and _cl_ok(x) and w_krsc.is_contiguous()
+    Ho, Wo = conv_out_hw(H, W, R, S, stride, pad)
+    y = empty_act(N, K, Ho, Wo, x.device)
+    g = _geom(N, H, W, C, K, R, S, stride, pad)
+    L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w_krsc), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
+                                  L.stream_ptr()), "conv_fwd")
+    return y
+
+
+def conv_dgrad(dy: torch.Tensor, w_krsc: torch.Tensor, x_shape, stride: int, pad: int) -> torch.Tensor:
+    N, C, H, W = x_shape
+    K, R, S, _ = w_krsc.shape
+    assert _cl_ok(dy)
+    dx = empty_act(N, C, H, W, dy.device)
+    g = _geom(N, H, W, C, K, R, S, stride, pad)
+    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.stream_ptr()), "conv_dgrad")
+    return dx
+
+
+def conv_wgrad_(dw_krsc_f32: torch.Tensor, x: torch.Tensor, dy: torch.Tensor, stride: int, pad: int,
+                max_splits: int = 0) -> None:
+    """dw [K,R,S,C] fp32 (contiguous storage) += wgrad(x, dy)."""
+    N, C, H, W = x.shape
+    K = dy.shape[1]
+    R, S = dw_krsc_f32.shape[1], dw_krsc_f32.shape[2]
+    assert _cl_ok(x) and _cl_ok(dy) and dw_krsc_f32.is_contiguous() and dw_krsc_f32.dtype == torch.float32
+    g = _geom(N, H, W, C, K, R, S, stride, pad)
+    L.check(L.lib().b200_conv_wgrad(L.ptr(x), L.ptr(dy), L.ptr(dw_krsc_f32), byref(g), c_int(max_splits),
+                                    L.stream_ptr()), "conv_wgrad")
+
+
+def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], relu: bool) -> torch.Tensor:
+    """x [M,K] bf16, w [N,K] bf16 -> y [M,N] bf16 (a 1x1 convolution on [M,1,1,K])."""
+    M, K = x.shape
+    N = w.shape[0]
+    assert x.is_contiguous() and w.is_contiguous()
+    y = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
+    L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
+                                  L.stream_ptr()), "linear_fwd")
+    return y
+
+
+def linear_dgrad(dy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    M, N = dy.shape
+    K = w.shape[1]
+    dx = torch.empty((M, K), dtype=torch.bfloat16, device=dy.device)
+    g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
+    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w), L.ptr(dx), byref(g), L.stream_ptr()), "linear_dgrad")
+    return dx
+
+
+def linear_wgrad_(dw_f32: torch.Tensor, x: torch.Tensor, dy: torch.Tensor) -> None:
+    M, K = x.shape
+    N = dy.shape[1]
+    assert dw_f32.is_contiguous() and dw_f32.dtype == torch.float32
+    g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
+    L.check(L.lib().b200_conv_wgrad(L.ptr(x), L.ptr(dy), L.ptr(dw_f32), byref(g), c_int(0), L.stream_ptr()), "linear_wgrad")
+
+
+# --------------------------------------------------------------------------------------------
+# batch norm (+ReLU +residual)
+# --------------------------------------------------------------------------------------------
+def _rows_c(x: torch.Tensor) -> Tuple[int, int]:
+    if x.dim() == 4:
+        n, c, h, w = x.shape
+        return n * h * w, c
+    return x.shape[0], x.shape[1]
+
+
+def bn_stats(x: torch.Tensor, gamma, beta, eps: float, momentum: float, running_mean, running_var) -> torch.Tensor:
+    rows, C = _rows_c(x)
+    stat = torch.empty((4, C), dtype=torch.float32, device=x.device)
+    sc = scratch(x.device)
+    L.check(L.lib().b200_bn_stats(L.ptr(x), c_size_t(rows), c_int(C), L.ptr(gamma), L.ptr(beta), c_float(eps),
+                                  c_float(momentum), L.ptr(stat), L.ptr(running_mean), L.ptr(running_var), L.ptr(sc),
+                                  c_size_t(sc.numel()), L.stream_ptr()), "bn_stats")
+    return stat
+
+
+def bn_eval_prep(gamma, beta, running_mean, running_var, eps: float) -> torch.Tensor:
+    C = gamma.numel()
+    stat = torch.empty((4, C), dtype=torch.float32, device=gamma.device)
+    L.check(L.lib().b200_bn_eval_prep(L.ptr(gamma), L.ptr(beta), L.ptr(running_mean), L.ptr(running_var), c_float(eps),
+                                      L.ptr(stat), c_int(C), L.stream_ptr()), "bn_eval_prep")
+    return stat
+
+
+def bn_apply(x: torch.Tensor, residual: Optional[torch.Tensor], stat: torch.Tensor, relu: bool) -> torch.Tensor:
+    rows, C = _rows_c(x)
+    y = torch.empty_like(x)
+    L.check(L.lib().b200_bn_apply(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(stat),
+                                  c_int(int(relu)), L.stream_ptr()), "bn_apply")
+    return y
+
+
+def bn_bwd(dy, x, y, stat, relu: bool, want_dres: bool, dgamma=None, dbeta=None, beta_accum: float = 0.0):
+    """Returns (dx, dres, sums[2,C]); dgamma/dbeta (if given) receive beta_accum*old + new."""
+    rows, C = _rows_c(x)
+    sums = torch.empty((2, C), dtype=torch.float32, device=x.device)
+    sc = scratch(x.device)
+    L.check(L.lib().b200_bn_bwd_reduce(L.ptr(dy), L.ptr(x), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(stat),
+                                       c_int(int(relu)), L.ptr(sums), L.ptr(dgamma), L.ptr(dbeta), c_float(beta_accum),
+                                       L.ptr(sc), c_size_t(sc.numel()), L.stream_ptr()), "bn_bwd_reduce")
+    dx = torch.empty_like(x)
+    dres = torch.empty_like(x) if want_dres else None
+    L.check(L.lib().b200_bn_bwd_apply(L.ptr(dy), L.ptr(x), L.ptr(y), L.ptr(dx), L.ptr(dres), c_size_t(rows), c_int(C),
+                                      L.ptr(stat), L.ptr(sums), c_int(int(relu)), L.stream_ptr()), "bn_bwd_apply")
+    return dx, dres, sums
+
+
+# --------------------------------------------------------------------------------------------
+# pools / relu
+# --------------------------------------------------------------------------------------------
+def maxpool_fwd(x: torch.Tensor, k: int, stride: int, pad: int):
+    N, C, H, W = x.shape
+    Ho, Wo = conv_out_hw(H, W, k, k, stride, pad)
+    y = empty_act(N, C, Ho, Wo, x.device)
+    amax = torch.empty((N, Ho, Wo, C), dtype=torch.uint8, device=x.device)
+    L.check(L.lib().b200_maxpool_fwd(L.ptr(x), L.ptr(y), L.ptr(amax), c_int(N), c_int(H), c_int(W), c_int(C), c_int(k),
+                                     c_int(stride), c_int(pad), L.stream_ptr()), "maxpool_fwd")
+    return y, amax
+
+
+def maxpool_bwd(dy: torch.Tensor, amax: torch.Tensor, x_shape, k: int, stride: int, pad: int) -> torch.Tensor:
+    N, C, H, W = x_shape
+    dx = empty_act(N, C, H, W, dy.device)
+    L.check(L.lib().b200_maxpool_bwd(L.ptr(dy), L.ptr(amax), L.ptr(dx), c_int(N), c_int(H), c_int(W), c_int(C), c_int(k),
+                                     c_int(stride), c_int(pad), L.stream_ptr()), "maxpool_bwd")
+    return dx
+
+
+def avgpool_fwd(x: torch.Tensor) -> torch.Tensor:
+    N, C, H, W = x.shape
+    y = torch.empty((N, C), dtype=torch.bfloat16, device=x.device)
+    L.check(L.lib().b200_avgpool_fwd(L.ptr(x), L.ptr(y), c_int(N), c_int(H * W), c_int(C), L.stream_ptr()), "avgpool_fwd")
+    return y
+
+
+def avgpool_bwd(dy: torch.Tensor, x_shape) -> torch.Tensor:
+    N, C, H, W = x_shape
+    dx = empty_act(N, C, H, W, dy.device)
+    L.check(L.lib().b200_avgpool_bwd(L.ptr(dy), L.ptr(dx), c_int(N), c_int(H * W), c_int(C), L.stream_ptr()), "avgpool_bwd")
+    return dx
+
+
+def relu_bwd(dy: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+    dx = torch.empty_like(dy)
+    L.check(L.lib().b200_relu_bwd(L.ptr(dy), L.ptr(y), L.ptr(dx), c_size_t(dy.numel()), L.stream_ptr()), "relu_bwd")
+    return dx
+
+
+# --------------------------------------------------------------------------------------------
+# losses / metrics
+# --------------------------------------------------------------------------------------------
+def softmax_xent(logits: torch.Tensor, targets: torch.Tensor, grad_scale: float, want_grad: bool = True):
+    """Returns (loss_mean fp32 scalar tensor, dlogits or None).  logits [B,C] fp32/bf16 contiguous."""
+    B, C = logits.shape
+    assert logits.is_contiguous() and targets.dtype == torch.int64
+    row_loss = torch.empty(B, dtype=torch.float32, device=logits.device)
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    dlogits = torch.empty_like(logits) if want_grad else None
+    sc = scratch(logits.device)
+    counter = sc[4096 - 64: 4096 - 60]      # a ticket word the BN counters never reach (they use [0, 4096-64))
+    L.check(L.lib().b200_softmax_xent(L.ptr(logits), c_int(L.dtype_code(logits.dtype)), L.ptr(targets), c_int(B), c_int(C),
+                                      L.ptr(row_loss), L.ptr(loss), L.ptr(dlogits), c_float(grad_scale), L.ptr(counter),
+                                      L.stream_ptr()), "softmax_xent")
+    return loss, dlogits
+
+
+def bce_logits(logits: torch.Tensor, targets: torch.Tensor, grad_scale: float, want_grad: bool = True):
+    n = logits.numel()
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    dlogits = torch.empty_like(logits) if want_grad else None
+    L.check(L.lib().b200_bce_logits(L.ptr(logits), c_int(L.dtype_code(logits.dtype)), L.ptr(targets), c_int(n), L.ptr(loss),
+                                    L.ptr(dlogits), c_float(grad_scale), L.stream_ptr()), "bce_logits")
+    return loss, dlogits
+
+
+def eval_count(logits: torch.Tensor, targets: torch.Tensor, correct: torch.Tensor, nll_sum: Optional[torch.Tensor]):
+    B, C = logits.shape
+    L.check(L.lib().b200_eval_count(L.ptr(logits), c_int(L.dtype_code(logits.dtype)), L.ptr(targets), c_int(B), c_int(C),
+                                    L.ptr(correct), L.ptr(nll_sum), L.stream_ptr()), "eval_count")
+
+
+# --------------------------------------------------------------------------------------------
+# optimizers over flat arenas
+# --------------------------------------------------------------------------------------------
+def sgd_step(p, g, m, shadow, lr, momentum, dampening, weight_decay, nesterov, grad_scale=1.0, zero_grad=True):
+    L.check(L.lib().b200_sgd_momentum(L.ptr(p), L.ptr(g), L.ptr(m), L.ptr(shadow), c_size_t(p.numel()), c_float(lr),
+                                      c_float(momentum), c_float(dampening), c_float(weight_decay), c_int(int(nesterov)),
+                                      c_float(grad_scale), c_int(int(zero_grad)), L.stream_ptr()), "sgd")
+
+
+def adam_step(p, g, m, v, shadow, lr, beta1, beta2, eps, weight_decay, step_dev, grad_scale=1.0, zero_grad=True):
+    L.check(L.lib().b200_step_inc(L.ptr(step_dev), L.stream_ptr()), "step_inc")
+    L.check(L.lib().b200_adam(L.ptr(p), L.ptr(g), L.ptr(m), L.ptr(v), L.ptr(shadow), c_size_t(p.numel()), c_float(lr),
+                              c_float(beta1), c_float(beta2), c_float(eps), c_float(weight_decay), L.ptr(step_dev),
+                              c_float(grad_scale), c_int(int(zero_grad)), L.stream_ptr()), "adam")
+
+
+def cast_bf16_(dst_bf16: torch.Tensor, src_f32: torch.Tensor):
+    L.check(L.lib().b200_cast_f32_to_bf16(L.ptr(src_f32), L.ptr(dst_bf16), c_size_t(src_f32.numel()), L.stream_ptr()), "cast")
+
+
+# --------------------------------------------------------------------------------------------
+# data: augmentation, trojan stamping
+# --------------------------------------------------------------------------------------------
+def augment(img_u8: torch.Tensor, offsets: Optional[torch.Tensor], mean: torch.Tensor, inv_std: torch.Tensor,
+            c_out: int = 8, pad: int = 4, nchw_fp32: bool = False) -> torch.Tensor:
+    """uint8 NHWC batch -> normalised activations (NHWC bf16 with zero-padded channels, or NCHW fp32)."""
+    N, H, W, C = img_u8.shape
+    assert img_u8.is_contiguous() and img_u8.dtype == torch.uint8
+    if nchw_fp32:
+        out = torch.empty((N, C, H, W), dtype=torch.float32, device=img_u8.device)
+        c_out = C
+    else:
+        out = empty_act(N, c_out, H, W, img_u8.device)
+    L.check(L.lib().b200_augment(L.ptr(img_u8), L.ptr(offsets), L.ptr(out), c_int(N), c_int(H), c_int(W), c_int(C),
+                                 c_int(c_out), c_int(pad), L.ptr(mean), L.ptr(inv_std), c_int(1 if nchw_fp32 else 0),
+                                 L.stream_ptr()), "augment")
+    return out
+
+
+def trojan_stamp_(x: torch.Tensor, pattern: torch.Tensor, loc_h: int, loc_w: int, alpha: float,
+                  mask: Optional[torch.Tensor] = None):
+    """In-place alpha-blend of ``pattern`` [PC,ph,pw] into x [N,C,H,W] fp32 at (loc_h, loc_w)."""
+    N, C, H, W = x.shape
+    PC, ph, pw = pattern.shape
+    assert x.is_contiguous() and x.dtype == torch.float32 and pattern.is_contiguous()
+    L.check(L.lib().b200_trojan_stamp(L.ptr(x), c_int(N), c_int(C), c_int(H), c_int(W), L.ptr(pattern), c_int(PC), c_int(ph),
+                                      c_int(pw), c_int(loc_h), c_int(loc_w), c_float(alpha), L.ptr(mask), L.stream_ptr()),
+            "trojan_stamp")

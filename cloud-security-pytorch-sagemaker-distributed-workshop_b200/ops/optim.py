@@ -1,0 +1,114 @@
+"""Fused optimizers: ``SGD`` with momentum and ``Adam`` with torch semantics.
+
+``optim.SGD(model.parameters(), lr=..., momentum=...)`` of the reference
+(``notebooks/code/cifar10-distributed-native-cpu.py:144``) and ``torch.optim.Adam(lr=1e-3)`` of the MNTD
+trainers (``notebooks/code/utils_basic.py:96``).  When the parameters live in a
+``DistributedDataParallel`` flat arena on a CUDA device the whole step is ONE kernel over the arena:
+it reads grad/param/state once, writes param/state, refreshes the bf16 shadow weights used by the
+tensor-core kernels and zeroes the gradient arena for the next backward.  Anything else (CPU, loose
+parameters) takes torch's own optimizer math — that is the CPU fallback, not a GPU code path.
+"""
+from __future__ import annotations
+
+from typing import Iterable
+
+import torch
+
+from . import native as nv
+
+
+def _owners(params):
+    owners = {}
+    loose = []
+    for p in params:
+        o = getattr(p, "_b200_owner", None)
+        o = o() if o is not None else None
+        if o is not None and p.is_cuda:
+            owners.setdefault(id(o), (o, []))[1].append(p)
+        else:
+            loose.append(p)
+    flat, rest = [], list(loose)
+    for o, ps in owners.values():
+        if len(ps) == len(o.params):
+            flat.append(o)
+        else:
+            rest.extend(ps)
+    return flat, rest
+
+
+class _FusedBase(torch.optim.Optimizer):
+    def _split(self):
+        params = [p for g in self.param_groups for p in g["params"]]
+        self._flat_owners, self._loose = _owners(params)
+
+    def zero_grad(self, set_to_none: bool = False):
+        """Arena gradients are views and are zeroed by ``step``; loose ones follow torch semantics."""
+        for p in self._loose:
+            if p.grad is not None:
+                if set_to_none:
+                    p.grad = None
+                else:
+                    p.grad.zero_()
+        for o in self._flat_owners:
+            if not getattr(o, "_grads_zeroed_by_step", False):
+                o.flat_grads.zero_()
+
+
+class SGD(_FusedBase):
+    def __init__(self, params: Iterable, lr: float = 0.01, momentum: float = 0.0, dampening: float = 0.0,
+                 weight_decay: float = 0.0, nesterov: bool = False):
+        defaults = dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay, nesterov=nesterov)
+        super().__init__(params, defaults)
+        if len(self.param_groups) != 1:
+            raise ValueError("b200ddp.optim.SGD takes a single parameter group")
+        self._split()
+        self._inner = torch.optim.SGD(self._loose, **defaults) if self._loose else None
+        self._momentum_flat = {}
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        g = self.param_groups[0]
+        for o in self._flat_owners:
+            m = self._momentum_flat.get(id(o))
+            if m is None and g["momentum"] != 0:
+                m = torch.zeros_like(o.flat_params)
+                self._momentum_flat[id(o)] = m
+            nv.sgd_step(o.flat_params, o.flat_grads, m, o.flat_shadow, g["lr"], g["momentum"], g["dampening"],
+                        g["weight_decay"], g["nesterov"], 1.0, True)
+            o._grads_zeroed_by_step = True
+        if self._inner is not None:
+            for k in ("lr", "momentum", "dampening", "weight_decay", "nesterov"):
+                self._inner.param_groups[0][k] = g[k]
+            self._inner.step()
+
+    def flat_state(self):
+        return {i: m for i, m in enumerate(self._momentum_flat.values())}
+
+
+class Adam(_FusedBase):
+    def __init__(self, params: Iterable, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0):
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
+        super().__init__(params, defaults)
+        if len(self.param_groups) != 1:
+            raise ValueError("b200ddp.optim.Adam takes a single parameter group")
+        self._split()
+        self._inner = torch.optim.Adam(self._loose, **defaults) if self._loose else None
+        self._state_flat = {}
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        g = self.param_groups[0]
+        for o in self._flat_owners:
+            st = self._state_flat.get(id(o))
+            if st is None:
+                st = (torch.zeros_like(o.flat_params), torch.zeros_like(o.flat_params),
+                      torch.zeros((), dtype=torch.int32, device=o.flat_params.device))
+                self._state_flat[id(o)] = st
+            nv.adam_step(o.flat_params, o.flat_grads, st[0], st[1], o.flat_shadow, g["lr"], g["betas"][0],
+                         g["betas"][1], g["eps"], g["weight_decay"], st[2], 1.0, True)
+            o._grads_zeroed_by_step = True
+        if self._inner is not None:
+            for k in ("lr", "betas", "eps", "weight_decay"):
+                self._inner.param_groups[0][k] = g[k]
+            self._inner.step()

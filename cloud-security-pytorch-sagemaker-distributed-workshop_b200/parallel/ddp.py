@@ -1,0 +1,244 @@
+"""``DistributedDataParallel`` — drop-in for ``torch.nn.parallel.DistributedDataParallel`` as the
+reference uses it (``notebooks/code/cifar10-distributed-native-cpu.py:141``,
+``cifar10-distributed-smddp-gpu.py:148``, ``train_basic_jumbo_distributed_cpu.py:61``,
+``train_basic_trojaned_distributed_cpu.py:64``).
+
+Semantics kept: rank-0 parameter+buffer broadcast at wrap time, gradient averaging over the world
+overlapped with backward, per-forward buffer (BN statistics) broadcast, ``no_sync()``, the
+``module.`` prefix on ``state_dict()`` keys, ``device_ids``/``output_device`` accepted (one device per
+process).
+
+Memory model (B200-first, laid out for one 180 GB HBM3e per rank):
+
+* ``flat_params``  fp32 master weights, one arena; ``param.data`` are views.  Conv weights are stored
+  in channels-last physical order (``[Cout][R][S][Cin]``) which is exactly what the implicit-GEMM
+  kernels want, while ``state_dict()`` still shows torch-shaped ``[Cout,Cin,R,S]`` tensors.
+* ``flat_grads``   fp32 gradient arena in *symmetric memory* (peer-mapped + NVLS multicast for
+  ``backend='b200'``); ``param.grad`` are views; buckets are byte ranges; native layers write their
+  weight gradient straight into their slot (no autograd accumulation kernel).
+* ``flat_shadow``  bf16 copy of ``flat_params`` maintained by the fused optimizer for the tensor-core
+  kernels.
+* ``flat_buffers`` every module buffer packed into one byte arena so the per-forward BN-stat sync
+  is a single broadcast.
+"""
+from __future__ import annotations
+
+import contextlib
+import weakref
+from typing import List, Optional
+
+import torch
+import torch.nn as nn
+
+from . import process_group as pg
+from .reducer import ALIGN_ELEMS, Reducer, assign_buckets
+from ..utils.config import CommConfig
+from ..utils.logging import get_logger
+
+log = get_logger(__name__)
+
+
+def _is_conv_weight(p: torch.Tensor) -> bool:
+    return p.dim() == 4
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, device_ids=None, output_device=None, dim: int = 0,
+                 broadcast_buffers: bool = True, process_group=None, bucket_cap_mb: Optional[float] = None,
+                 find_unused_parameters: bool = False, gradient_as_bucket_view: bool = True,
+                 static_graph: bool = True, direct_grad_sink: bool = True, shadow_dtype=torch.bfloat16):
+        super().__init__()
+        self.module = module
+        self.broadcast_buffers = broadcast_buffers
+        self.world_size = pg.get_world_size()
+        self.rank = pg.get_rank()
+        self.backend = pg.get_backend() or "local"
+        self.comm = pg.get_comm()
+        self.cfg = CommConfig()
+        if bucket_cap_mb is not None:
+            self.cfg.bucket_cap_mb = float(bucket_cap_mb)
+        self.require_backward_grad_sync = True
+        self._accum_count = 0
+        self._callback_queued = False
+        self.direct_grad_sink = direct_grad_sink
+
+        params = [p for p in module.parameters() if p.requires_grad]
+        if not params:
+            raise RuntimeError("DistributedDataParallel: module has no parameter that requires grad")
+        self.device = params[0].device
+        if self.backend == "b200" and self.device.type != "cuda":
+            raise RuntimeError("backend 'b200' needs the module on a CUDA device (call .to(device) first)")
+        for p in params:
+            if p.dtype != torch.float32:
+                raise RuntimeError("DistributedDataParallel keeps fp32 master parameters; got %s" % p.dtype)
+
+        # ---- arena layout: reverse registration order == the order backward produces grads
+        self.params: List[nn.Parameter] = list(reversed(params))
+        numels = [p.numel() for p in self.params]
+        offsets, buckets, total = assign_buckets(
+            numels, int(self.cfg.first_bucket_mb * 1024 * 1024), int(self.cfg.bucket_cap_mb * 1024 * 1024))
+        self.offsets, self.buckets, self.total_elems = offsets, buckets, total
+        param_bucket = [0] * len(self.params)
+        for b in buckets:
+            for i in b.param_ids:
+                param_bucket[i] = b.index
+
+        # ---- flat arenas
+        self.flat_params = torch.zeros(total, dtype=torch.float32, device=self.device)
+        grad_off_bytes = 0
+        if self.backend == "b200" and self.world_size >= 1 and self.comm is not None:
+            self.flat_grads, grad_off_bytes = self.comm.alloc_arena(total, torch.float32)
+        else:
+            self.flat_grads = torch.zeros(total, dtype=torch.float32, device=self.device)
+        self.flat_shadow = None
+        if self.device.type == "cuda" and shadow_dtype is not None:
+            self.flat_shadow = torch.zeros(total, dtype=shadow_dtype, device=self.device)
+
+        with torch.no_grad():
+            for i, p in enumerate(self.params):
+                off, n = offsets[i], p.numel()
+                cl = _is_conv_weight(p)
+                src = p.detach()
+                if cl:   # channels-last physical layout, torch-shaped logical view
+                    co, ci, r, s = p.shape
+                    slot = self.flat_params[off: off + n].view(co, r, s, ci).permute(0, 3, 1, 2)
+                    gslot = self.flat_grads[off: off + n].view(co, r, s, ci).permute(0, 3, 1, 2)
+                else:
+                    slot = self.flat_params[off: off + n].view(p.shape)
+                    gslot = self.flat_grads[off: off + n].view(p.shape)
+                slot.copy_(src)
+                p.data = slot
+                p.grad = gslot
+                p._b200_slot = (off, n)                      # arena slot (elements)
+                p._b200_owner = weakref.ref(self)
+                if self.flat_shadow is not None:
+                    sh = self.flat_shadow[off: off + n]
+                    p._b200_shadow = sh.view(co, r, s, ci) if cl else sh.view(p.shape)
+                if direct_grad_sink:
+                    p._b200_sink = _GradSink(self, i, self.flat_grads[off: off + n])
+        self._grad_views = [p.grad for p in self.params]
+        self.refresh_shadow()
+
+        # ---- buffers: one byte arena so the per-forward sync is one broadcast
+        self._setup_buffers()
+
+        self.reducer = Reducer(self.flat_grads, buckets, param_bucket, self.world_size,
+                               self.backend, comm=self.comm, arena_offset_bytes=grad_off_bytes)
+        for i, p in enumerate(self.params):
+            p.register_post_accumulate_grad_hook(self._make_hook(i))
+
+        # ---- wrap-time sync from rank 0 (params + buffers), like the reference's DDP ctor
+        if self.world_size > 1:
+            pg.broadcast(self.flat_params, src=0)
+            if self.flat_buffers is not None:
+                pg.broadcast(self.flat_buffers, src=0)
+            self.refresh_shadow()
+        if self.cfg.debug or True:
+            sizes = ", ".join("%d B (%d tensors)" % (sum(numels[i] for i in b.param_ids) * 4, len(b.param_ids))
+                              for b in buckets)
+            log.debug("b200ddp.DDP: %d params, %d elements, %d bucket(s): %s", len(self.params),
+                      sum(numels), len(buckets), sizes)
+
+    # ------------------------------------------------------------------ buffers
+    def _setup_buffers(self):
+        bufs = [b for b in self.module.buffers()]
+        self._buffers_list = bufs
+        self.flat_buffers = None
+        if not bufs:
+            return
+        offs, cur = [], 0
+        for b in bufs:
+            offs.append(cur)
+            cur += (b.numel() * b.element_size() + 255) // 256 * 256
+        if self.backend == "b200" and self.comm is not None and self.world_size > 1:
+            flat, _ = self.comm.alloc_arena(cur, torch.uint8)
+        else:
+            flat = torch.zeros(cur, dtype=torch.uint8, device=self.device)
+        with torch.no_grad():
+            for b, off in zip(bufs, offs):
+                nbytes = b.numel() * b.element_size()
+                view = flat[off: off + nbytes].view(b.dtype).view(b.shape)
+                view.copy_(b)
+                b.data = view
+        self.flat_buffers = flat
+
+    # ------------------------------------------------------------------ hooks
+    def _make_hook(self, idx: int):
+        def hook(param):
+            view = self._grad_views[idx]
+            g = param.grad
+            if g is not None and g.data_ptr() != view.data_ptr():
+                # someone dropped our view (zero_grad(set_to_none=True)): copy in and re-point
+                if self._accum_count > 0 or self.reducer.was_written(idx):
+                    view.add_(g)
+                else:
+                    view.copy_(g)
+                param.grad = view
+            self._on_grad_ready(idx)
+        return hook
+
+    def _on_grad_ready(self, idx: int):
+        if not self._callback_queued:
+            self._callback_queued = True
+            self.reducer.prepare_for_backward()
+            self.reducer.require_sync = self.require_backward_grad_sync
+            from torch.autograd import Variable
+            Variable._execution_engine.queue_callback(self._finalize_backward)
+        self.reducer.mark_ready(idx)
+
+    def _finalize_backward(self):
+        self._callback_queued = False
+        self.reducer.finalize()
+        if self.require_backward_grad_sync:
+            self._accum_count = 0
+        else:
+            self._accum_count += 1
+
+    # ------------------------------------------------------------------ module API
+    def forward(self, *args, **kwargs):
+        if (self.broadcast_buffers and self.world_size > 1 and self.flat_buffers is not None
+                and self.require_backward_grad_sync and self.training):
+            pg.broadcast(self.flat_buffers, src=0)       # KB12: one coalesced broadcast
+        return self.module(*args, **kwargs)
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    def zero_grad(self, set_to_none: bool = False):   # grads are arena views: zero, never free
+        self.flat_grads.zero_()
+        self._accum_count = 0
+
+    def refresh_shadow(self):
+        """Re-derive the bf16 shadow weights from the fp32 masters (after load_state_dict etc.)."""
+        if self.flat_shadow is not None:
+            self.flat_shadow.copy_(self.flat_params)
+
+    def grad_beta(self, idx: int) -> float:
+        """0.0 -> the native layer overwrites its gradient slot, 1.0 -> it accumulates."""
+        return 1.0 if (self._accum_count > 0 or self.reducer.was_written(idx)) else 0.0
+
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        out = super().load_state_dict(state_dict, strict=strict)
+        self.refresh_shadow()
+        return out
+
+
+class _GradSink:
+    """Handle a native layer uses to deposit its weight gradient directly in the arena."""
+
+    __slots__ = ("ddp", "idx", "flat")
+
+    def __init__(self, ddp: DistributedDataParallel, idx: int, flat: torch.Tensor):
+        self.ddp, self.idx, self.flat = ddp, idx, flat
+
+    def beta(self) -> float:
+        return self.ddp.grad_beta(self.idx)
+
+    def done(self):
+        self.ddp._on_grad_ready(self.idx)

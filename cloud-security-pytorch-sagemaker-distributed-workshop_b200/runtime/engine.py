@@ -1,0 +1,129 @@
+"""Train-step engine: the hot loop of the reference's trainers
+(``notebooks/code/cifar10-distributed-smddp-gpu.py:162-168``: H2D copy, ``zero_grad``, forward, loss,
+``backward``, ``optimizer.step``) as ONE CUDA-graph replay per step.
+
+On a GPU the whole step — GPU-side augmentation of the uint8 batch, forward, fused loss, backward with
+the bucketed gradient all-reduce forked onto the comm stream, fused optimizer — is captured once and
+replayed; per step the host only copies the next batch (uint8 pixels, labels, crop offsets) from
+pinned memory into the graph's static input buffers and reads the loss back when asked.  Without a GPU
+(or with ``graph=False``) the same step runs eagerly, which is the CPU/gloo fallback path.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from ..nn import modules as bmod
+from ..ops import functional as BF
+from ..utils.data import CIFAR10_MEAN, CIFAR10_STD, augment_reference
+
+
+class TrainStep:
+    def __init__(self, model: nn.Module, criterion: Callable, optimizer, batch_size: int, image_shape=(32, 32, 3),
+                 device: Optional[torch.device] = None, graph: bool = True, augment: bool = True,
+                 mean=CIFAR10_MEAN, std=CIFAR10_STD, seed: int = 0, warmup_iters: int = 3):
+        self.model, self.criterion, self.optimizer = model, criterion, optimizer
+        self.device = torch.device(device) if device is not None else next(model.parameters()).device
+        self.cuda = self.device.type == "cuda"
+        self.batch_size = int(batch_size)
+        self.image_shape = tuple(image_shape)
+        self.augment = augment
+        self.use_graph = bool(graph) and self.cuda
+        self.rng = np.random.RandomState(seed)
+        self.warmup_iters = warmup_iters
+        self.steps_done = 0
+        self._graph = None
+        self._captured_batch = None
+        self.mean_t = torch.tensor(mean, dtype=torch.float32, device=self.device)
+        self.inv_std_t = 1.0 / torch.tensor(std, dtype=torch.float32, device=self.device)
+        self._mean, self._std = mean, std
+        if self.cuda:
+            H, W, C = self.image_shape
+            B = self.batch_size
+            self.static_x = torch.zeros((B, H, W, C), dtype=torch.uint8, device=self.device)
+            self.static_y = torch.zeros((B,), dtype=torch.int64, device=self.device)
+            self.static_off = torch.zeros((B, 3), dtype=torch.int32, device=self.device)
+            self.static_loss = torch.zeros((), dtype=torch.float32, device=self.device)
+            self.pin_off = torch.zeros((B, 3), dtype=torch.int32).pin_memory()
+            self.pin_loss = torch.zeros((), dtype=torch.float32).pin_memory()
+            BF.assume_unit_loss_grad(True)
+            bmod.defer_bn_counters(True)
+
+    # ------------------------------------------------------------------ one step, eager
+    def _draw_offsets(self, n: int) -> torch.Tensor:
+        off = np.stack([self.rng.randint(0, 9, n), self.rng.randint(0, 9, n), self.rng.randint(0, 2, n)], 1)
+        return torch.from_numpy(off.astype(np.int32))
+
+    def _body(self, x_u8, y, offsets):
+        from ..ops import native as nv
+        if self.cuda:
+            cin = 8
+            inp = nv.augment(x_u8, offsets if self.augment else None, self.mean_t, self.inv_std_t, c_out=cin)
+        else:
+            inp = augment_reference(x_u8, train_transform=self.augment, mean=self._mean, std=self._std, offsets=offsets)
+        self.optimizer.zero_grad()
+        out = self.model(inp)
+        loss = self.criterion(out, y)
+        loss.backward()
+        self.optimizer.step()
+        return loss
+
+    # ------------------------------------------------------------------ graph capture
+    def _capture(self):
+        s = torch.cuda.Stream(device=self.device)
+        s.wait_stream(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(s):
+            for _ in range(self.warmup_iters):       # also runs one-time setup (func attributes, buffers)
+                loss = self._body(self.static_x, self.static_y, self.static_off)
+                self.static_loss.copy_(loss.detach())
+        torch.cuda.current_stream(self.device).wait_stream(s)
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            loss = self._body(self.static_x, self.static_y, self.static_off)
+            self.static_loss.copy_(loss.detach())
+        self._graph = g
+        self.steps_done += self.warmup_iters       # warm-up iterations were real optimizer steps
+
+    # ------------------------------------------------------------------ public
+    def __call__(self, x_u8: torch.Tensor, y: torch.Tensor, need_loss: bool = False):
+        """Run one optimisation step on a uint8 NHWC batch (host-pinned, device or CPU tensors).
+        Returns the loss as a Python float when ``need_loss`` (a D2H read), else ``None``."""
+        n = x_u8.shape[0]
+        offsets = self._draw_offsets(n) if self.augment else None
+        if not self.cuda:
+            loss = self._body(x_u8, y, offsets)
+            self.steps_done += 1
+            return float(loss.item()) if need_loss else None
+        if self.use_graph and n == self.batch_size:
+            if self._graph is None:
+                self.static_x.copy_(x_u8, non_blocking=True)
+                self.static_y.copy_(y, non_blocking=True)
+                self._capture()
+            self.static_x.copy_(x_u8, non_blocking=True)
+            self.static_y.copy_(y, non_blocking=True)
+            if offsets is not None:
+                self.pin_off.copy_(offsets)
+                self.static_off.copy_(self.pin_off, non_blocking=True)
+            self._graph.replay()
+            self.steps_done += 1
+            if need_loss:
+                self.pin_loss.copy_(self.static_loss, non_blocking=True)
+                torch.cuda.current_stream(self.device).synchronize()
+                return float(self.pin_loss.item())
+            return None
+        # eager path (last short batch of an epoch, or graph=False)
+        xd = x_u8.to(self.device, non_blocking=True)
+        yd = y.to(self.device, non_blocking=True)
+        od = offsets.to(self.device, non_blocking=True) if offsets is not None else None
+        loss = self._body(xd, yd, od)
+        self.steps_done += 1
+        return float(loss.item()) if need_loss else None
+
+    def flush_counters(self):
+        if self.cuda:
+            bmod.flush_bn_counters(self.model, self.steps_done - getattr(self, "_flushed", 0))
+            self._flushed = self.steps_done

@@ -1,0 +1,332 @@
+// Training-mode batch normalisation fused with ReLU and the residual add, NHWC bf16.
+//
+// Replaces cuDNN BatchNorm fwd/bwd + ATen relu/add for the 20 BN layers of torchvision resnet18 the
+// reference trains (notebooks/code/cifar10-distributed-smddp-gpu.py:32; KB2/KB7 in SURVEY §2.5).
+//
+// Activations are [rows = N*H*W][C] bf16.  A CTA owns one 64-channel group (128 contiguous bytes per
+// row = one cache line) and a strided set of rows: thread (v, rl) handles channels 8v..8v+7 of rows
+// rl, rl+32, ...   Per-channel reductions are two-level and deterministic: CTA partials go to scratch,
+// the last CTA of a channel group (ticket counter, self-resetting) sums them in fixed order and
+// finalises (mean/rstd/scale/shift + running statistics, or dgamma/dbeta).  No atomics on data, no
+// memset, CUDA-graph replayable.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kVL = 8;                  // 16-byte vector lanes per row  -> 64 channels per CTA
+constexpr int kRL = kThreads / kVL;     // 32 row lanes
+constexpr int kGroup = kVL * 8;         // 64 channels
+
+__device__ __forceinline__ bf16x8 ld_vec(const __nv_bfloat16* p) { return *reinterpret_cast<const bf16x8*>(p); }
+__device__ __forceinline__ void st_vec(__nv_bfloat16* p, const bf16x8& v) { *reinterpret_cast<bf16x8*>(p) = v; }
+
+// reduce acc0/acc1 ([8] per thread) over the 32 row lanes; thread t<128 gets channel (t&63) of array (t>>6)
+__device__ __forceinline__ float cta_reduce_rows(const float* a0, const float* a1, float (*sm)[kRL][kGroup]) {
+  const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sm[0][rl][v * 8 + k] = a0[k];
+    sm[1][rl][v * 8 + k] = a1[k];
+  }
+  __syncthreads();
+  float tot = 0.f;
+  if (threadIdx.x < 2 * kGroup) {
+    const int which = threadIdx.x >> 6, ch = threadIdx.x & 63;
+#pragma unroll 8
+    for (int r = 0; r < kRL; ++r) tot += sm[which][r][ch];
+  }
+  return tot;
+}
+
+// returns true in every thread of the last CTA of this channel group
+__device__ __forceinline__ bool publish_and_elect(float tot, float* partial, unsigned* counters) {
+  __shared__ bool last;
+  const int RB = gridDim.x, rb = blockIdx.x, cg = blockIdx.y;
+  if (threadIdx.x < 2 * kGroup) partial[((size_t)cg * RB + rb) * (2 * kGroup) + threadIdx.x] = tot;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned ticket = atomicAdd(counters + cg, 1u);
+    last = (ticket == (unsigned)RB - 1);
+    if (last) counters[cg] = 0u;
+  }
+  __syncthreads();
+  if (last) __threadfence();
+  return last;
+}
+
+__device__ __forceinline__ float sum_partials(const float* partial) {
+  const int RB = gridDim.x, cg = blockIdx.y;
+  float t = 0.f;
+  for (int rb = 0; rb < RB; ++rb) t += __ldcg(partial + ((size_t)cg * RB + rb) * (2 * kGroup) + threadIdx.x);
+  return t;
+}
+
+__global__ void __launch_bounds__(kThreads)
+bn_stats_kernel(const __nv_bfloat16* __restrict__ x, size_t rows, int C, const float* __restrict__ gamma,
+                const float* __restrict__ beta, float eps, float momentum, float* __restrict__ stat /*[4][C]*/,
+                float* __restrict__ running_mean, float* __restrict__ running_var, float* __restrict__ partial,
+                unsigned* __restrict__ counters) {
+  __shared__ float sm[2][kRL][kGroup];
+  __shared__ float fin[2][kGroup];
+  const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
+  const int c = blockIdx.y * kGroup + v * 8;
+  float s[8], q[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
+  if (c < C) {
+    for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
+      float f[8];
+      bf16x8_to_float(ld_vec(x + r * C + c), f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        s[k] += f[k];
+        q[k] = fmaf(f[k], f[k], q[k]);
+      }
+    }
+  }
+  const float tot = cta_reduce_rows(s, q, sm);
+  if (!publish_and_elect(tot, partial, counters)) return;
+  if (threadIdx.x < 2 * kGroup) fin[threadIdx.x >> 6][threadIdx.x & 63] = sum_partials(partial);
+  __syncthreads();
+  if (threadIdx.x < kGroup) {
+    const int ch = blockIdx.y * kGroup + threadIdx.x;
+    if (ch < C) {
+      const float inv_n = 1.f / (float)rows;
+      const float mean = fin[0][threadIdx.x] * inv_n;
+      const float var = fmaxf(fin[1][threadIdx.x] * inv_n - mean * mean, 0.f);
+      const float rstd = rsqrtf(var + eps);
+      const float sc = gamma[ch] * rstd;
+      stat[ch] = mean;
+      stat[C + ch] = rstd;
+      stat[2 * C + ch] = sc;
+      stat[3 * C + ch] = beta[ch] - mean * sc;
+      if (running_mean != nullptr) {
+        const float unbiased = rows > 1 ? var * (float)rows / (float)(rows - 1) : var;
+        running_mean[ch] = (1.f - momentum) * running_mean[ch] + momentum * mean;
+        running_var[ch] = (1.f - momentum) * running_var[ch] + momentum * unbiased;
+      }
+    }
+  }
+}
+
+__global__ void bn_eval_prep_kernel(const float* gamma, const float* beta, const float* rm, const float* rv, float eps,
+                                    float* stat, int C) {
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ch >= C) return;
+  const float rstd = rsqrtf(rv[ch] + eps), sc = gamma[ch] * rstd;
+  stat[ch] = rm[ch];
+  stat[C + ch] = rstd;
+  stat[2 * C + ch] = sc;
+  stat[3 * C + ch] = beta[ch] - rm[ch] * sc;
+}
+
+template <bool kRelu, bool kRes>
+__global__ void __launch_bounds__(kThreads)
+bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
+                __nv_bfloat16* __restrict__ y, size_t rows, int C, const float* __restrict__ stat) {
+  const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
+  const int c = blockIdx.y * kGroup + v * 8;
+  if (c >= C) return;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sc[k] = stat[2 * C + c + k];
+    sh[k] = stat[3 * C + c + k];
+  }
+  for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
+    float f[8];
+    bf16x8_to_float(ld_vec(x + r * C + c), f);
+    float rr[8];
+    if (kRes) bf16x8_to_float(ld_vec(res + r * C + c), rr);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float o = fmaf(f[k], sc[k], sh[k]);
+      if (kRes) o += rr[k];
+      if (kRelu) o = fmaxf(o, 0.f);
+      f[k] = o;
+    }
+    st_vec(y + r * C + c, float_to_bf16x8(f));
+  }
+}
+
+template <bool kRelu>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                     const __nv_bfloat16* __restrict__ y, size_t rows, int C, const float* __restrict__ stat,
+                     float* __restrict__ sums /*[2][C]*/, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                     float beta_accum, float* __restrict__ partial, unsigned* __restrict__ counters) {
+  __shared__ float sm[2][kRL][kGroup];
+  const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
+  const int c = blockIdx.y * kGroup + v * 8;
+  float s[8], q[8], mean[8], rstd[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
+  if (c < C) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      mean[k] = stat[c + k];
+      rstd[k] = stat[C + c + k];
+    }
+    for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
+      float g[8], xv[8], yv[8];
+      bf16x8_to_float(ld_vec(dy + r * C + c), g);
+      bf16x8_to_float(ld_vec(x + r * C + c), xv);
+      if (kRelu) bf16x8_to_float(ld_vec(y + r * C + c), yv);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float gg = (kRelu && !(yv[k] > 0.f)) ? 0.f : g[k];
+        s[k] += gg;
+        q[k] = fmaf(gg, (xv[k] - mean[k]) * rstd[k], q[k]);
+      }
+    }
+  }
+  const float tot = cta_reduce_rows(s, q, sm);
+  if (!publish_and_elect(tot, partial, counters)) return;
+  if (threadIdx.x < 2 * kGroup) {
+    const float t = sum_partials(partial);
+    const int which = threadIdx.x >> 6, ch = blockIdx.y * kGroup + (threadIdx.x & 63);
+    if (ch < C) {
+      sums[which * C + ch] = t;
+      float* dst = which == 0 ? dbeta : dgamma;
+      if (dst != nullptr) dst[ch] = beta_accum != 0.f ? fmaf(beta_accum, dst[ch], t) : t;
+    }
+  }
+}
+
+template <bool kRelu, bool kRes>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx,
+                    __nv_bfloat16* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
+                    const float* __restrict__ sums) {
+  const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
+  const int c = blockIdx.y * kGroup + v * 8;
+  if (c >= C) return;
+  const float inv_n = 1.f / (float)rows;
+  float mean[8], rstd[8], a[8], m1[8], m2[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    mean[k] = stat[c + k];
+    rstd[k] = stat[C + c + k];
+    a[k] = stat[2 * C + c + k];  // gamma * rstd
+    m1[k] = sums[c + k] * inv_n;
+    m2[k] = sums[C + c + k] * inv_n;
+  }
+  for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
+    float g[8], xv[8], yv[8];
+    bf16x8_to_float(ld_vec(dy + r * C + c), g);
+    bf16x8_to_float(ld_vec(x + r * C + c), xv);
+    if (kRelu) bf16x8_to_float(ld_vec(y + r * C + c), yv);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float gg = (kRelu && !(yv[k] > 0.f)) ? 0.f : g[k];
+      g[k] = gg;
+      xv[k] = a[k] * (gg - m1[k] - (xv[k] - mean[k]) * rstd[k] * m2[k]);
+    }
+    st_vec(dx + r * C + c, float_to_bf16x8(xv));
+    if (kRes) st_vec(dres + r * C + c, float_to_bf16x8(g));
+  }
+}
+
+dim3 bn_grid(size_t rows, int C, int per_sm) {
+  const int cg = (C + kGroup - 1) / kGroup;
+  size_t rb = (rows + kRL - 1) / kRL;
+  size_t cap = (size_t)b200_num_sms() * per_sm / cg;
+  if (cap < 1) cap = 1;
+  if (rb > cap) rb = cap;
+  if (rb < 1) rb = 1;
+  return dim3((unsigned)rb, (unsigned)cg, 1);
+}
+
+}  // namespace
+
+// scratch layout: [counters: 1024 x u32][partials: CG * RB * 128 floats]
+static constexpr size_t kCounterBytes = 4096;
+
+extern "C" size_t b200_bn_scratch_bytes(size_t rows, int C) {
+  dim3 g = bn_grid(rows, C, 4);
+  return kCounterBytes + (size_t)g.x * g.y * 2 * kGroup * sizeof(float);
+}
+
+extern "C" int b200_bn_stats(const void* x_bf16, size_t rows, int C, const float* gamma, const float* beta, float eps,
+                             float momentum, float* stat, float* running_mean, float* running_var, void* scratch,
+                             size_t scratch_bytes, void* stream) {
+  B200_REQUIRE(x_bf16 && gamma && beta && stat && scratch, "null argument");
+  B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
+  B200_REQUIRE((C + kGroup - 1) / kGroup <= 1024, "too many channel groups");
+  B200_REQUIRE(scratch_bytes >= b200_bn_scratch_bytes(rows, C), "scratch too small (b200_bn_scratch_bytes)");
+  dim3 g = bn_grid(rows, C, 4);
+  bn_stats_kernel<<<g, kThreads, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x_bf16, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var,
+      (float*)((char*)scratch + kCounterBytes), (unsigned*)scratch);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int b200_bn_eval_prep(const float* gamma, const float* beta, const float* running_mean,
+                                 const float* running_var, float eps, float* stat, int C, void* stream) {
+  B200_REQUIRE(gamma && beta && running_mean && running_var && stat && C > 0, "bad argument");
+  bn_eval_prep_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(gamma, beta, running_mean, running_var, eps, stat, C);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int b200_bn_apply(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C,
+                             const float* stat, int relu, void* stream) {
+  B200_REQUIRE(x_bf16 && y_bf16 && stat, "null argument");
+  B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
+  dim3 g = bn_grid(rows, C, 8);
+  cudaStream_t s = (cudaStream_t)stream;
+  const __nv_bfloat16 *x = (const __nv_bfloat16*)x_bf16, *r = (const __nv_bfloat16*)residual_bf16;
+  __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
+  if (relu && r) bn_apply_kernel<true, true><<<g, kThreads, 0, s>>>(x, r, y, rows, C, stat);
+  else if (relu) bn_apply_kernel<true, false><<<g, kThreads, 0, s>>>(x, r, y, rows, C, stat);
+  else if (r) bn_apply_kernel<false, true><<<g, kThreads, 0, s>>>(x, r, y, rows, C, stat);
+  else bn_apply_kernel<false, false><<<g, kThreads, 0, s>>>(x, r, y, rows, C, stat);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int b200_bn_bwd_reduce(const void* dy_bf16, const void* x_bf16, const void* y_bf16, size_t rows, int C,
+                                  const float* stat, int relu, float* sums, float* dgamma, float* dbeta,
+                                  float beta_accum, void* scratch, size_t scratch_bytes, void* stream) {
+  B200_REQUIRE(dy_bf16 && x_bf16 && stat && sums && scratch, "null argument");
+  B200_REQUIRE(!relu || y_bf16, "relu mask needs y");
+  B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
+  B200_REQUIRE(scratch_bytes >= b200_bn_scratch_bytes(rows, C), "scratch too small (b200_bn_scratch_bytes)");
+  dim3 g = bn_grid(rows, C, 4);
+  cudaStream_t s = (cudaStream_t)stream;
+  float* partial = (float*)((char*)scratch + kCounterBytes);
+  unsigned* counters = (unsigned*)scratch;
+  if (relu)
+    bn_bwd_reduce_kernel<true><<<g, kThreads, 0, s>>>((const __nv_bfloat16*)dy_bf16, (const __nv_bfloat16*)x_bf16,
+                                                     (const __nv_bfloat16*)y_bf16, rows, C, stat, sums, dgamma, dbeta,
+                                                     beta_accum, partial, counters);
+  else
+    bn_bwd_reduce_kernel<false><<<g, kThreads, 0, s>>>((const __nv_bfloat16*)dy_bf16, (const __nv_bfloat16*)x_bf16,
+                                                      (const __nv_bfloat16*)y_bf16, rows, C, stat, sums, dgamma, dbeta,
+                                                      beta_accum, partial, counters);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int b200_bn_bwd_apply(const void* dy_bf16, const void* x_bf16, const void* y_bf16, void* dx_bf16,
+                                 void* dres_bf16, size_t rows, int C, const float* stat, const float* sums, int relu,
+                                 void* stream) {
+  B200_REQUIRE(dy_bf16 && x_bf16 && dx_bf16 && stat && sums, "null argument");
+  B200_REQUIRE(!relu || y_bf16, "relu mask needs y");
+  B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
+  dim3 g = bn_grid(rows, C, 8);
+  cudaStream_t s = (cudaStream_t)stream;
+  const __nv_bfloat16 *dy = (const __nv_bfloat16*)dy_bf16, *x = (const __nv_bfloat16*)x_bf16,
+                      *y = (const __nv_bfloat16*)y_bf16;
+  __nv_bfloat16 *dx = (__nv_bfloat16*)dx_bf16, *dr = (__nv_bfloat16*)dres_bf16;
+  if (relu && dr) bn_bwd_apply_kernel<true, true><<<g, kThreads, 0, s>>>(dy, x, y, dx, dr, rows, C, stat, sums);
+  else if (relu) bn_bwd_apply_kernel<true, false><<<g, kThreads, 0, s>>>(dy, x, y, dx, dr, rows, C, stat, sums);
+  else if (dr) bn_bwd_apply_kernel<false, true><<<g, kThreads, 0, s>>>(dy, x, y, dx, dr, rows, C, stat, sums);
+  else bn_bwd_apply_kernel<false, false><<<g, kThreads, 0, s>>>(dy, x, y, dx, dr, rows, C, stat, sums);
+  B200_CHECK_LAUNCH();
+  return 0;
+}

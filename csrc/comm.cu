@@ -1,0 +1,422 @@
+// Fused gradient all-reduce / broadcast / barrier over NVLink 5 + NVSwitch, written for sm_100a.
+//
+// These kernels replace the NCCL ring all-reduce that the reference reaches through
+// smdistributed.dataparallel (notebooks/code/cifar10-distributed-smddp-gpu.py:148,167; job log
+// notebooks/2_pytorch_dist_smddp_gpu.ipynb:350-400 "24 coll channels ... via P2P/IPC/read") and the
+// separate "divide by world size" pass of the DDP Reducer.  There is no NCCL call here: every rank
+// maps every peer's arena (csrc/symm.cu) and the kernels issue the NVLink loads/stores themselves.
+//
+//   one-shot  (W1)  every rank reads all peers' copies, reduces in registers (fp32, fixed rank order
+//                   -> bitwise identical on all ranks), scales, writes its own copy.  In place, with a
+//                   mid barrier between "all reads done" and "first write".
+//   two-shot  (W2)  rank r reduces shard r from all peers (reduce-scatter by pull) and PUSHES the scaled
+//                   result into every peer's arena (all-gather by posted stores): 2 barriers total.
+//   NVLS      (W3)  rank r issues multimem.ld_reduce on the multicast address of shard r (the switch
+//                   sums all N copies), scales, multimem.st broadcasts the result to all N arenas.
+//   broadcast (W4)  pull from the root's arena.       barrier (W5)  flag exchange on the signal pads.
+//
+// Synchronisation: per-CTA flag barrier on the signal pads (first MiB of every arena).  Block b of rank
+// a writes epoch e into slot [e&1][b][a] of every peer (st.release.sys) and spins on its own slots
+// (ld.acquire.sys) until all peers wrote e.  Epochs live in device memory, so the kernels are CUDA-graph
+// replayable.  A spin that exceeds timeout_ns raises the host-mapped error flag and falls through
+// instead of hanging (SURVEY §5.3 failure detection).
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 512;
+constexpr int kSigInts = 2 * B200_MAX_COMM_BLOCKS * B200_MAX_RANKS;  // flags region, uint32
+// layout of the signal MiB:  [0, kSigInts*4) flags | [64 KiB, 64 KiB + blocks*4) epochs (local only)
+constexpr size_t kEpochOff = 64 * 1024;
+
+__device__ __forceinline__ uint32_t* sig_slot(char* base, uint32_t phase, int block, int src) {
+  return reinterpret_cast<uint32_t*>(base) + ((phase * B200_MAX_COMM_BLOCKS + block) * B200_MAX_RANKS + src);
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// All threads of the CTA must call this.  Orders every earlier memory operation of the CTA before the
+// flag (release, system scope) and every later one after the peers' flags (acquire).
+__device__ __forceinline__ void cta_barrier_all_ranks(const b200_comm& c) {
+  __threadfence_system();
+  __syncthreads();
+  uint32_t* epochs = reinterpret_cast<uint32_t*>(c.peer[c.rank] + kEpochOff);
+  const uint32_t e = epochs[blockIdx.x] + 1;
+  if (threadIdx.x < c.world) {
+    const int r = threadIdx.x;
+    st_release_sys(sig_slot(c.peer[r], e & 1u, blockIdx.x, c.rank), e);
+    const uint32_t* mine = sig_slot(c.peer[c.rank], e & 1u, blockIdx.x, r);
+    if (ld_acquire_sys(mine) != e) {
+      const unsigned long long t0 = globaltimer_ns();
+      unsigned spins = 0;
+      while (ld_acquire_sys(mine) != e) {
+        if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > c.timeout_ns) {
+          if (c.err_flag) {
+            c.err_flag[0] = 1;
+            c.err_flag[1] = r;            // which peer never arrived
+            c.err_flag[2] = (int)blockIdx.x;
+          }
+          break;
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) epochs[blockIdx.x] = e;
+}
+
+// ---- 16-byte vector traits -----------------------------------------------------------------------
+template <int DT>
+struct Vec;
+template <>
+struct Vec<B200_DTYPE_F32> {
+  static constexpr int kElems = 4;
+  __device__ static void accumulate(float* acc, const int4& raw) {
+    const float* f = reinterpret_cast<const float*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[i] += f[i];
+  }
+  __device__ static int4 pack(const float* acc, float scale) {
+    int4 o;
+    float* f = reinterpret_cast<float*>(&o);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) f[i] = acc[i] * scale;
+    return o;
+  }
+  __device__ static int4 mc_ld_reduce(const void* mc) {
+    int4 o;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(o.x), "=r"(o.y), "=r"(o.z), "=r"(o.w)
+                 : "l"(mc)
+                 : "memory");
+    return o;
+  }
+};
+template <>
+struct Vec<B200_DTYPE_BF16> {
+  static constexpr int kElems = 8;
+  __device__ static void accumulate(float* acc, const int4& raw) {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      float2 f = __bfloat1622float2(h[i]);
+      acc[2 * i] += f.x;
+      acc[2 * i + 1] += f.y;
+    }
+  }
+  __device__ static int4 pack(const float* acc, float scale) {
+    int4 o;
+    __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(acc[2 * i] * scale, acc[2 * i + 1] * scale);
+    return o;
+  }
+  __device__ static int4 mc_ld_reduce(const void* mc) {
+    int4 o;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(o.x), "=r"(o.y), "=r"(o.z), "=r"(o.w)
+                 : "l"(mc)
+                 : "memory");
+    return o;
+  }
+};
+
+__device__ __forceinline__ int4 ld_peer(const void* p) {  // peer data is written by other GPUs: no .nc
+  int4 v;
+  asm volatile("ld.relaxed.sys.global.v4.s32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer(void* p, const int4& v) {
+  asm volatile("st.relaxed.sys.global.v4.s32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void mc_st(void* mc, const int4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
+
+// ---- W1 one-shot ----------------------------------------------------------------------------------
+// `out` is a local buffer (may be the local arena itself: in place).  Reads of a round complete on all
+// ranks (mid barrier) before anyone overwrites, so in-place use is race free.
+template <int DT, int WORLD, int UNROLL>
+__global__ void __launch_bounds__(kThreads, 1)
+allreduce_oneshot_kernel(b200_comm c, size_t offset, char* out, size_t chunks, float scale, int need_mid_barrier) {
+  using V = Vec<DT>;
+  cta_barrier_all_ranks(c);  // every peer entered: its gradients for this bucket are final
+  const size_t per_round = (size_t)gridDim.x * kThreads * UNROLL;
+  for (size_t base = (size_t)blockIdx.x * kThreads * UNROLL; base < chunks; base += per_round) {
+    float acc[UNROLL][V::kElems];
+    int4 raw[WORLD][UNROLL];
+#pragma unroll
+    for (int r = 0; r < WORLD; ++r) {
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
+        raw[r][u] = make_int4(0, 0, 0, 0);
+        if (idx < chunks) raw[r][u] = ld_peer(c.peer[r] + offset + idx * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+#pragma unroll
+      for (int i = 0; i < V::kElems; ++i) acc[u][i] = 0.f;
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) V::accumulate(acc[u], raw[r][u]);  // fixed order 0..N-1
+    }
+    if (need_mid_barrier) cta_barrier_all_ranks(c);
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
+      if (idx < chunks) *reinterpret_cast<int4*>(out + idx * 16) = V::pack(acc[u], scale);
+    }
+  }
+  if (!need_mid_barrier) cta_barrier_all_ranks(c);  // out-of-place: protect the arena from early reuse
+}
+
+// ---- W2 two-shot (pull-reduce + push-broadcast) and W3 NVLS ---------------------------------------
+template <int DT, int WORLD, int UNROLL, bool NVLS>
+__global__ void __launch_bounds__(kThreads, 1)
+allreduce_shard_kernel(b200_comm c, size_t offset, size_t chunks, float scale) {
+  using V = Vec<DT>;
+  // equal 16-byte-chunk shards, independent of tensor boundaries ("balanced fusion buffer")
+  const size_t per = (chunks + WORLD - 1) / WORLD;
+  const size_t lo = (size_t)c.rank * per;
+  const size_t hi = lo + per < chunks ? lo + per : chunks;
+  cta_barrier_all_ranks(c);
+  const size_t per_round = (size_t)gridDim.x * kThreads * UNROLL;
+  for (size_t base = lo + (size_t)blockIdx.x * kThreads * UNROLL; base < hi; base += per_round) {
+    if constexpr (NVLS) {
+      int4 red[UNROLL];
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
+        if (idx < hi) red[u] = V::mc_ld_reduce(c.mc + offset + idx * 16);
+      }
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
+        if (idx < hi) {
+          float acc[V::kElems];
+#pragma unroll
+          for (int i = 0; i < V::kElems; ++i) acc[i] = 0.f;
+          V::accumulate(acc, red[u]);
+          mc_st(c.mc + offset + idx * 16, V::pack(acc, scale));
+        }
+      }
+    } else {
+      int4 raw[WORLD][UNROLL];
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) {
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
+          raw[r][u] = make_int4(0, 0, 0, 0);
+          if (idx < hi) raw[r][u] = ld_peer(c.peer[r] + offset + idx * 16);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
+        if (idx < hi) {
+          float acc[V::kElems];
+#pragma unroll
+          for (int i = 0; i < V::kElems; ++i) acc[i] = 0.f;
+#pragma unroll
+          for (int r = 0; r < WORLD; ++r) V::accumulate(acc, raw[r][u]);
+          const int4 o = V::pack(acc, scale);
+#pragma unroll
+          for (int i = 0; i < WORLD; ++i) {
+            const int p = (c.rank + i) % WORLD;  // stagger destinations across ranks
+            st_peer(c.peer[p] + offset + idx * 16, o);
+          }
+        }
+      }
+    }
+  }
+  cta_barrier_all_ranks(c);  // all pushed / multicast stores have landed everywhere
+}
+
+// ---- W4 broadcast (pull) --------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 1) broadcast_kernel(b200_comm c, size_t offset, size_t chunks, int root) {
+  cta_barrier_all_ranks(c);  // root's data is final, receivers' buffers are free
+  if (c.rank != root) {
+    const char* src = c.peer[root] + offset;
+    char* dst = c.peer[c.rank] + offset;
+    const size_t stride = (size_t)gridDim.x * kThreads;
+    for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < chunks; i += stride)
+      *reinterpret_cast<int4*>(dst + i * 16) = ld_peer(src + i * 16);
+  }
+  cta_barrier_all_ranks(c);  // root may overwrite again
+}
+
+__global__ void __launch_bounds__(kThreads, 1) barrier_kernel(b200_comm c) { cta_barrier_all_ranks(c); }
+
+template <typename T>
+__global__ void scale_kernel(T* p, size_t n, float scale);
+template <>
+__global__ void scale_kernel<float>(float* p, size_t n, float scale) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) p[i] *= scale;
+}
+template <>
+__global__ void scale_kernel<__nv_bfloat16>(__nv_bfloat16* p, size_t n, float scale) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    p[i] = __float2bfloat16(__bfloat162float(p[i]) * scale);
+}
+
+int clamp_blocks(size_t work_chunks, int unroll, int max_blocks) {
+  size_t need = (work_chunks + (size_t)kThreads * unroll - 1) / ((size_t)kThreads * unroll);
+  if (max_blocks <= 0 || max_blocks > B200_MAX_COMM_BLOCKS) max_blocks = B200_MAX_COMM_BLOCKS;
+  if (need < 1) need = 1;
+  if (need > (size_t)max_blocks) need = max_blocks;
+  return (int)need;
+}
+
+template <int DT, int WORLD>
+int launch_world(const b200_comm& c, size_t offset, size_t chunks, float scale, int algo, int max_blocks,
+                 cudaStream_t s) {
+  if (algo == B200_ALGO_ONESHOT) {
+    constexpr int U = (WORLD <= 4) ? 4 : 2;
+    int blocks = clamp_blocks(chunks, U, max_blocks);
+    allreduce_oneshot_kernel<DT, WORLD, U><<<blocks, kThreads, 0, s>>>(c, offset, c.peer[c.rank] + offset, chunks, scale, 1);
+  } else if (algo == B200_ALGO_NVLS) {
+    constexpr int U = 4;
+    int blocks = clamp_blocks((chunks + WORLD - 1) / WORLD, U, max_blocks);
+    allreduce_shard_kernel<DT, WORLD, U, true><<<blocks, kThreads, 0, s>>>(c, offset, chunks, scale);
+  } else {
+    constexpr int U = (WORLD <= 4) ? 4 : 2;
+    int blocks = clamp_blocks((chunks + WORLD - 1) / WORLD, U, max_blocks);
+    allreduce_shard_kernel<DT, WORLD, U, false><<<blocks, kThreads, 0, s>>>(c, offset, chunks, scale);
+  }
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+template <int DT>
+int launch_dtype(const b200_comm& c, size_t offset, size_t chunks, float scale, int algo, int max_blocks,
+                 cudaStream_t s) {
+  switch (c.world) {
+    case 2: return launch_world<DT, 2>(c, offset, chunks, scale, algo, max_blocks, s);
+    case 3: return launch_world<DT, 3>(c, offset, chunks, scale, algo, max_blocks, s);
+    case 4: return launch_world<DT, 4>(c, offset, chunks, scale, algo, max_blocks, s);
+    case 5: return launch_world<DT, 5>(c, offset, chunks, scale, algo, max_blocks, s);
+    case 6: return launch_world<DT, 6>(c, offset, chunks, scale, algo, max_blocks, s);
+    case 7: return launch_world<DT, 7>(c, offset, chunks, scale, algo, max_blocks, s);
+    case 8: return launch_world<DT, 8>(c, offset, chunks, scale, algo, max_blocks, s);
+    default: b200_set_error("world size %d not in 2..8", c.world); return B200_ERR_ARG;
+  }
+}
+
+template <int DT, int WORLD>
+int launch_oneshot_out(const b200_comm& c, size_t offset, char* out, size_t chunks, float scale, int max_blocks,
+                       cudaStream_t s) {
+  constexpr int U = (WORLD <= 4) ? 4 : 2;
+  int blocks = clamp_blocks(chunks, U, max_blocks);
+  const int in_place = (out == c.peer[c.rank] + offset) ? 1 : 0;
+  allreduce_oneshot_kernel<DT, WORLD, U><<<blocks, kThreads, 0, s>>>(c, offset, out, chunks, scale, in_place);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+}  // namespace
+
+static size_t elem_size(int dtype) { return dtype == B200_DTYPE_BF16 ? 2 : 4; }
+
+extern "C" int b200_allreduce(const b200_comm* comm, size_t offset, size_t count, int dtype, float scale, int algo,
+                              int max_blocks, void* stream) {
+  B200_REQUIRE(comm != nullptr, "null communicator");
+  B200_REQUIRE(dtype == B200_DTYPE_F32 || dtype == B200_DTYPE_BF16, "dtype must be f32 or bf16");
+  B200_REQUIRE(offset % 16 == 0, "offset must be 16-byte aligned");
+  B200_REQUIRE((count * elem_size(dtype)) % 16 == 0, "byte count must be a multiple of 16 (pad the bucket)");
+  B200_REQUIRE(offset >= B200_SIGNAL_BYTES, "offset overlaps the signal region");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (count == 0) return 0;
+  const b200_comm& c = *comm;
+  if (c.world == 1) {
+    if (scale != 1.0f) {
+      unsigned g = b200_grid_for(count, 256, 8);
+      if (dtype == B200_DTYPE_F32)
+        scale_kernel<float><<<g, 256, 0, s>>>((float*)(c.peer[0] + offset), count, scale);
+      else
+        scale_kernel<__nv_bfloat16><<<g, 256, 0, s>>>((__nv_bfloat16*)(c.peer[0] + offset), count, scale);
+      B200_CHECK_LAUNCH();
+    }
+    return 0;
+  }
+  const size_t bytes = count * elem_size(dtype);
+  const size_t chunks = bytes / 16;
+  if (algo == B200_ALGO_AUTO) algo = (bytes <= 64 * 1024) ? B200_ALGO_ONESHOT : (c.mc ? B200_ALGO_NVLS : B200_ALGO_TWOSHOT);
+  if (algo == B200_ALGO_NVLS && c.mc == nullptr) {
+    b200_set_error("NVLS requested but no multicast mapping is bound");
+    return B200_ERR_UNSUPPORTED;
+  }
+  return dtype == B200_DTYPE_F32 ? launch_dtype<B200_DTYPE_F32>(c, offset, chunks, scale, algo, max_blocks, s)
+                                 : launch_dtype<B200_DTYPE_BF16>(c, offset, chunks, scale, algo, max_blocks, s);
+}
+
+extern "C" int b200_allreduce_oneshot_out(const b200_comm* comm, size_t offset, void* out, size_t count, int dtype,
+                                          float scale, int max_blocks, void* stream) {
+  B200_REQUIRE(comm != nullptr && out != nullptr, "null argument");
+  B200_REQUIRE(offset % 16 == 0 && ((uintptr_t)out) % 16 == 0, "16-byte alignment required");
+  B200_REQUIRE((count * elem_size(dtype)) % 16 == 0, "byte count must be a multiple of 16");
+  const b200_comm& c = *comm;
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t chunks = count * elem_size(dtype) / 16;
+  if (c.world == 1) {
+    B200_CHECK_CUDA(cudaMemcpyAsync(out, c.peer[0] + offset, chunks * 16, cudaMemcpyDeviceToDevice, s));
+    return 0;
+  }
+#define B200_OS(DT)                                                                                         \
+  switch (c.world) {                                                                                        \
+    case 2: return launch_oneshot_out<DT, 2>(c, offset, (char*)out, chunks, scale, max_blocks, s);          \
+    case 3: return launch_oneshot_out<DT, 3>(c, offset, (char*)out, chunks, scale, max_blocks, s);          \
+    case 4: return launch_oneshot_out<DT, 4>(c, offset, (char*)out, chunks, scale, max_blocks, s);          \
+    case 5: return launch_oneshot_out<DT, 5>(c, offset, (char*)out, chunks, scale, max_blocks, s);          \
+    case 6: return launch_oneshot_out<DT, 6>(c, offset, (char*)out, chunks, scale, max_blocks, s);          \
+    case 7: return launch_oneshot_out<DT, 7>(c, offset, (char*)out, chunks, scale, max_blocks, s);          \
+    case 8: return launch_oneshot_out<DT, 8>(c, offset, (char*)out, chunks, scale, max_blocks, s);          \
+    default: break;                                                                                         \
+  }
+  if (dtype == B200_DTYPE_F32) {
+    B200_OS(B200_DTYPE_F32)
+  } else {
+    B200_OS(B200_DTYPE_BF16)
+  }
+#undef B200_OS
+  b200_set_error("world size %d not in 1..8", c.world);
+  return B200_ERR_ARG;
+}
+
+extern "C" int b200_broadcast(const b200_comm* comm, size_t offset, size_t bytes, int root, int max_blocks,
+                              void* stream) {
+  B200_REQUIRE(comm != nullptr, "null communicator");
+  B200_REQUIRE(offset % 16 == 0 && bytes % 16 == 0, "offset/bytes must be multiples of 16");
+  B200_REQUIRE(root >= 0 && root < comm->world, "bad root");
+  if (comm->world == 1 || bytes == 0) return 0;
+  int blocks = clamp_blocks(bytes / 16, 4, max_blocks);
+  broadcast_kernel<<<blocks, kThreads, 0, (cudaStream_t)stream>>>(*comm, offset, bytes / 16, root);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int b200_barrier(const b200_comm* comm, void* stream) {
+  B200_REQUIRE(comm != nullptr, "null communicator");
+  if (comm->world == 1) return 0;
+  barrier_kernel<<<1, kThreads, 0, (cudaStream_t)stream>>>(*comm);
+  B200_CHECK_LAUNCH();
+  return 0;
+}

@@ -1,0 +1,167 @@
+/*
+ * b200ddp — C ABI of the native library (libb200ddp.so).
+ *
+ * Everything the Python layer calls goes through these entry points (ctypes).  All pointers are
+ * device pointers unless a name says "host"; every launch function takes the CUDA stream to launch
+ * on (as a void*, i.e. a cudaStream_t) and returns 0 on success or a negative b200 error / a positive
+ * cudaError_t.  b200_last_error() gives the text of the last failure on the calling thread.
+ *
+ * The reference (Neela08/cloud-security-pytorch-sagemaker-distributed-workshop) has no native code of
+ * its own; each group below names the external native library call it replaces on the reference's hot
+ * path and the reference line that reaches it.
+ */
+#ifndef B200DDP_H_
+#define B200DDP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_MAX_RANKS 8
+#define B200_MAX_COMM_BLOCKS 64
+#define B200_SIGNAL_BYTES (1u << 20) /* first MiB of every symmetric arena: signal pads + epochs */
+
+#define B200_DTYPE_F32 0
+#define B200_DTYPE_BF16 1
+
+const char* b200_last_error(void);
+int b200_version(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * Symmetric memory (replaces NCCL's P2P/IPC buffer registration; notebooks/2_*.ipynb:400
+ * "via P2P/IPC/read").  cuMemCreate + POSIX-fd export, peer import/map, NVSwitch multicast object.
+ * ------------------------------------------------------------------------------------------- */
+int b200_symm_init(int device);
+int b200_symm_granularity(int device, size_t* gran_out, size_t* mc_gran_out);
+int b200_symm_alloc(int device, size_t bytes, void** ptr_out, int* fd_out, uint64_t* handle_out);
+int b200_symm_import(int device, int fd, size_t bytes, void** ptr_out, uint64_t* handle_out);
+int b200_symm_unmap(void* ptr, size_t bytes, uint64_t handle);
+int b200_mc_supported(int device);
+int b200_mc_create(int ndev, size_t bytes, uint64_t* mc_handle_out, int* fd_out);
+int b200_mc_import(int fd, uint64_t* mc_handle_out);
+int b200_mc_add_device(uint64_t mc_handle, int device);
+int b200_mc_bind_map(int device, uint64_t mc_handle, uint64_t mem_handle, size_t bytes, void** mc_ptr_out);
+int b200_mc_release(int device, uint64_t mc_handle, void* mc_ptr, size_t bytes);
+int b200_close_fd(int fd);
+
+/* Communicator context: peer base pointers of the symmetric arena (peer[rank] is the local
+ * mapping), multicast base (or NULL), host-mapped error flag.  Passed by value to the kernels. */
+typedef struct b200_comm {
+  int rank;
+  int world;
+  char* peer[B200_MAX_RANKS];
+  char* mc;
+  int* err_flag;               /* device pointer to a host-mapped int; non-zero => spin timeout */
+  unsigned long long timeout_ns;
+} b200_comm;
+
+int b200_comm_alloc_errflag(int** host_ptr_out, int** dev_ptr_out);
+
+/* ---------------------------------------------------------------------------------------------
+ * Collectives over the symmetric arena (replace NCCL ring allreduce/broadcast under SMDDP —
+ * cifar10-distributed-smddp-gpu.py:148,167; notebooks/2_*.ipynb:350-400).  Offsets are bytes from the
+ * arena base and must be 16-byte aligned; `count` is elements of `dtype`.  All fuse `* scale`
+ * (gradient averaging) into the reduction.  `algo`: 0 auto, 1 one-shot, 2 two-shot (P2P
+ * reduce + push), 3 NVLS (multimem.ld_reduce + multimem.st).  `max_blocks` caps the grid.
+ * ------------------------------------------------------------------------------------------- */
+#define B200_ALGO_AUTO 0
+#define B200_ALGO_ONESHOT 1
+#define B200_ALGO_TWOSHOT 2
+#define B200_ALGO_NVLS 3
+int b200_allreduce(const b200_comm* comm, size_t offset, size_t count, int dtype, float scale,
+                   int algo, int max_blocks, void* stream);
+/* One-shot all-reduce from the symmetric arena into an arbitrary local buffer (out-of-place). */
+int b200_allreduce_oneshot_out(const b200_comm* comm, size_t offset, void* out, size_t count, int dtype,
+                               float scale, int max_blocks, void* stream);
+int b200_broadcast(const b200_comm* comm, size_t offset, size_t bytes, int root, int max_blocks, void* stream);
+int b200_barrier(const b200_comm* comm, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Optimizers over flat arenas (replace ATen foreach SGD / Adam — …native-cpu.py:144,156;
+ * utils_basic.py:96).  p/g/m/v are fp32; shadow (may be NULL) receives the bf16 copy of p.
+ * ------------------------------------------------------------------------------------------- */
+int b200_sgd_momentum(float* p, float* g, float* m, void* shadow_bf16, size_t n, float lr, float momentum,
+                      float dampening, float weight_decay, int nesterov, float grad_scale, int zero_grad,
+                      void* stream);
+int b200_adam(float* p, float* g, float* m, float* v, void* shadow_bf16, size_t n, float lr, float beta1,
+              float beta2, float eps, float weight_decay, const int* step_dev, float grad_scale,
+              int zero_grad, void* stream);
+int b200_step_inc(int* step_dev, void* stream);
+int b200_cast_f32_to_bf16(const float* src, void* dst_bf16, size_t n, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Losses / metrics (replace ATen log_softmax+nll_loss, BCE-with-logits, argmax/eq/sum —
+ * …native-cpu.py:143,152,185-187; model_lib/rtNLP_cnn_model.py:64).
+ * ------------------------------------------------------------------------------------------- */
+int b200_softmax_xent(const void* logits, int dtype, const int64_t* targets, int rows, int cols,
+                      float* row_loss, float* loss_mean, void* dlogits, float grad_scale,
+                      unsigned int* scratch_counter, void* stream);
+int b200_bce_logits(const void* logits, int dtype, const float* targets, int n, float* loss_mean,
+                    void* dlogits, float grad_scale, void* stream);
+int b200_eval_count(const void* logits, int dtype, const int64_t* targets, int rows, int cols,
+                    int* correct_out, float* nll_sum_out, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Batch norm (+ReLU, +residual), pools, augmentation — NHWC bf16 activations
+ * (replace cuDNN BN / ATen relu, add, pools — torchvision resnet18 under …smddp-gpu.py:32).
+ * ------------------------------------------------------------------------------------------- */
+/* Scratch contract of the BN reductions: `scratch` is global memory beyond the op's inputs/outputs
+ * (CTA partial sums + ticket counters).  It must be zero before its first use; every launch leaves
+ * the counters at zero again.  Size: b200_bn_scratch_bytes(rows, C). */
+size_t b200_bn_scratch_bytes(size_t rows, int C);
+/* stat is [4][C] fp32: mean, rstd, scale = gamma*rstd, shift = beta - mean*scale. */
+int b200_bn_stats(const void* x_bf16, size_t rows, int C, const float* gamma, const float* beta, float eps,
+                  float momentum, float* stat, float* running_mean, float* running_var, void* scratch,
+                  size_t scratch_bytes, void* stream);
+int b200_bn_eval_prep(const float* gamma, const float* beta, const float* running_mean,
+                      const float* running_var, float eps, float* stat, int C, void* stream);
+int b200_bn_apply(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C,
+                  const float* stat, int relu, void* stream);
+/* sums is [2][C]: sum(g), sum(g*xhat) with g = dy * relu_mask; dgamma/dbeta (may be NULL) are written
+ * as beta_accum*old + new, i.e. straight into the flat gradient arena. */
+int b200_bn_bwd_reduce(const void* dy_bf16, const void* x_bf16, const void* y_bf16, size_t rows, int C,
+                       const float* stat, int relu, float* sums, float* dgamma, float* dbeta,
+                       float beta_accum, void* scratch, size_t scratch_bytes, void* stream);
+int b200_bn_bwd_apply(const void* dy_bf16, const void* x_bf16, const void* y_bf16, void* dx_bf16,
+                      void* dres_bf16, size_t rows, int C, const float* stat, const float* sums, int relu,
+                      void* stream);
+int b200_maxpool_fwd(const void* x, void* y, uint8_t* argmax, int N, int H, int W, int C, int k, int stride,
+                     int pad, void* stream);
+int b200_maxpool_bwd(const void* dy, const uint8_t* argmax, void* dx, int N, int H, int W, int C, int k,
+                     int stride, int pad, void* stream);
+int b200_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int b200_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
+int b200_relu_bwd(const void* dy, const void* y, void* dx, size_t n, void* stream);
+/* layout 0: out = NHWC bf16 with C_out >= C channels (zero padded); layout 1: NCHW fp32.
+ * offsets [N][3] int32 = (crop dy, crop dx in 0..2*pad, flip) or NULL for the identity crop. */
+int b200_augment(const uint8_t* img_u8, const int32_t* offsets, void* out, int N, int H, int W, int C,
+                 int C_out, int pad, const float* mean, const float* inv_std, int layout, void* stream);
+/* x is NCHW fp32; pattern [pattern_channels][p_h][p_w], pattern_channels in {1, C}; mask[N] (or NULL). */
+int b200_trojan_stamp(float* x, int N, int C, int H, int W, const float* pattern, int pattern_channels,
+                      int p_h, int p_w, int loc_h, int loc_w, float alpha, const uint8_t* mask, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Tensor-core layers: implicit-GEMM convolution and linear (a 1x1 convolution on [M,1,1,K]) on
+ * tcgen05 + TMEM (replace cuDNN conv fwd/dgrad/wgrad and cuBLAS GEMM under nn.Conv2d / nn.Linear —
+ * torchvision resnet18 via …smddp-gpu.py:32; model_lib/cifar10_cnn_model.py:11-18).
+ * x: NHWC bf16 [N][H][W][C]; w: bf16 [K][R][S][C]; y/dy: NHWC bf16 [N][Ho][Wo][K]; dw: fp32 [K][R][S][C].
+ * C and K must be multiples of 8.  b200_conv_wgrad ACCUMULATES into dw (fp32 red.add, split-K).
+ * ------------------------------------------------------------------------------------------- */
+typedef struct b200_conv_geom {
+  int N, H, W, C; /* input */
+  int K;          /* output channels */
+  int R, S, stride, pad;
+} b200_conv_geom;
+int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g, int relu,
+                  void* stream);
+int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream);
+int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
+                    void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DDP_H_ */
