@@ -1,0 +1,261 @@
+"""Numerics of every native kernel against a plain PyTorch fp32 reference of the same op (GPU)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+CL = torch.channels_last
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    return torch.device("cuda", 0)
+
+
+def _act(n, c, h, w, dev, scale=1.0):
+    x = (torch.randn(n, c, h, w, device=dev) * scale).to(torch.bfloat16).contiguous(memory_format=CL)
+    return x
+
+
+def _rel_err(a, b):
+    a, b = a.float(), b.float()
+    return float((a - b).norm() / (b.norm() + 1e-12))
+
+
+CONV_CASES = [
+    # N, C, H, W, K, R, stride, pad
+    (4, 64, 8, 8, 64, 3, 1, 1),
+    (2, 64, 8, 8, 128, 3, 2, 1),
+    (8, 128, 4, 4, 128, 3, 1, 1),
+    (32, 256, 2, 2, 512, 3, 2, 1),
+    (32, 512, 1, 1, 512, 3, 1, 1),
+    (4, 64, 8, 8, 128, 1, 2, 0),
+    (2, 8, 32, 32, 64, 7, 2, 3),
+    (3, 16, 14, 14, 8, 5, 1, 0),
+    (2, 32, 17, 13, 72, 3, 1, 1),
+    (2, 64, 56, 56, 64, 3, 1, 1),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES)
+def test_conv_fwd_dgrad_wgrad(case):
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    torch.manual_seed(0)
+    N, C, H, W, K, R, stride, pad = case
+    x = _act(N, C, H, W, dev)
+    w = (torch.randn(K, C, R, R, device=dev) / (C * R * R) ** 0.5)
+    w_krsc = w.permute(0, 2, 3, 1).contiguous().to(torch.bfloat16)
+    bias = torch.randn(K, device=dev)
+    xr = x.float().requires_grad_(True)
+    wr = w_krsc.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    yr = F.conv2d(xr, wr, bias, stride=stride, padding=pad)
+    y = nv.conv_fwd(x, w_krsc, bias, stride, pad, relu=False)
+    assert y.shape == yr.shape
+    assert _rel_err(y, yr) < 1e-2, "fwd"
+    yrelu = nv.conv_fwd(x, w_krsc, bias, stride, pad, relu=True)
+    assert _rel_err(yrelu, F.relu(yr)) < 1e-2, "fwd+relu"
+    dy = _act(*yr.shape, dev)
+    yr.backward(dy.float())
+    dx = nv.conv_dgrad(dy, w_krsc, x.shape, stride, pad)
+    assert _rel_err(dx, xr.grad) < 1e-2, "dgrad"
+    dw = torch.zeros(K, R, R, C, device=dev)
+    nv.conv_wgrad_(dw, x, dy, stride, pad)
+    assert _rel_err(dw.permute(0, 3, 1, 2), wr.grad) < 1e-2, "wgrad"
+    nv.conv_wgrad_(dw, x, dy, stride, pad)      # accumulates
+    assert _rel_err(dw.permute(0, 3, 1, 2), 2 * wr.grad) < 1e-2, "wgrad accumulate"
+
+
+@pytest.mark.parametrize("M,K,N", [(32, 512, 1000), (256, 400, 120), (100, 4096, 256), (7, 88, 16), (300, 2048, 1000)])
+def test_linear(M, K, N):
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    torch.manual_seed(1)
+    x = torch.randn(M, K, device=dev).to(torch.bfloat16)
+    w = (torch.randn(N, K, device=dev) / K ** 0.5).to(torch.bfloat16)
+    b = torch.randn(N, device=dev)
+    y = nv.linear_fwd(x, w, b, relu=False)
+    yr = F.linear(x.float(), w.float(), b)
+    assert _rel_err(y, yr) < 1e-2
+    dy = torch.randn(M, N, device=dev).to(torch.bfloat16)
+    dx = nv.linear_dgrad(dy, w)
+    assert _rel_err(dx, dy.float() @ w.float()) < 1e-2
+    dw = torch.zeros(N, K, device=dev)
+    nv.linear_wgrad_(dw, x, dy)
+    assert _rel_err(dw, dy.float().t() @ x.float()) < 1e-2
+
+
+@pytest.mark.parametrize("shape,relu,res", [((8, 64, 8, 8), True, False), ((8, 128, 4, 4), True, True),
+                                            ((32, 512, 1, 1), False, False), ((4, 256, 14, 14), True, True),
+                                            ((2, 64, 112, 112), True, False)])
+def test_batchnorm(shape, relu, res):
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    torch.manual_seed(2)
+    N, C, H, W = shape
+    x = _act(N, C, H, W, dev, 2.0)
+    r = _act(N, C, H, W, dev) if res else None
+    gamma = torch.rand(C, device=dev) + 0.5
+    beta = torch.randn(C, device=dev)
+    rm, rv = torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    rm_ref, rv_ref = rm.clone(), rv.clone()
+    stat = nv.bn_stats(x, gamma, beta, 1e-5, 0.1, rm, rv)
+    y = nv.bn_apply(x, r, stat, relu)
+    xr = x.float().requires_grad_(True)
+    gr, br = gamma.clone().requires_grad_(True), beta.clone().requires_grad_(True)
+    rr = r.float().requires_grad_(True) if res else None
+    yr = F.batch_norm(xr, rm_ref, rv_ref, gr, br, True, 0.1, 1e-5)
+    if res:
+        yr = yr + rr
+    if relu:
+        yr = F.relu(yr)
+    assert _rel_err(y, yr) < 1e-2
+    assert torch.allclose(rm, rm_ref, atol=1e-3, rtol=1e-3) and torch.allclose(rv, rv_ref, atol=1e-3, rtol=1e-3)
+    dy = _act(N, C, H, W, dev)
+    # the oracle must see the same ReLU mask as the kernel (mask from the bf16 output)
+    g = dy.float() * ((y.float() > 0).float() if relu else 1.0)
+    pre = F.batch_norm(xr, None, None, gr, br, True, 0.1, 1e-5)
+    if res:
+        pre = pre + rr
+    pre.backward(g)
+    dgamma, dbeta = torch.zeros(C, device=dev), torch.zeros(C, device=dev)
+    dx, dres, sums = nv.bn_bwd(dy, x, y, stat, relu, res, dgamma, dbeta, 1.0)
+    assert _rel_err(dx, xr.grad) < 2e-2
+    assert _rel_err(dgamma, gr.grad) < 1e-2 and _rel_err(dbeta, br.grad) < 1e-2
+    if res:
+        assert _rel_err(dres, rr.grad) < 1e-2
+    # scratch is self-resetting: a second launch gives the same statistics
+    stat2 = nv.bn_stats(x, gamma, beta, 1e-5, 0.1, None, None)
+    assert torch.equal(stat, stat2)
+
+
+def test_bn_eval():
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    x = _act(4, 64, 8, 8, dev)
+    g, b = torch.rand(64, device=dev) + 0.5, torch.randn(64, device=dev)
+    rm, rv = torch.randn(64, device=dev), torch.rand(64, device=dev) + 0.5
+    y = nv.bn_apply(x, None, nv.bn_eval_prep(g, b, rm, rv, 1e-5), False)
+    assert _rel_err(y, F.batch_norm(x.float(), rm, rv, g, b, False, 0.1, 1e-5)) < 1e-2
+
+
+@pytest.mark.parametrize("k,s,p,shape", [(3, 2, 1, (4, 64, 16, 16)), (2, 2, 0, (4, 8, 28, 28)), (2, 2, 0, (3, 16, 10, 10))])
+def test_maxpool(k, s, p, shape):
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    x = _act(*shape, dev)
+    xr = x.float().requires_grad_(True)
+    yr = F.max_pool2d(xr, k, s, p)
+    y, am = nv.maxpool_fwd(x, k, s, p)
+    assert torch.equal(y.float(), yr)
+    dy = _act(*yr.shape, dev)
+    yr.backward(dy.float())
+    dx = nv.maxpool_bwd(dy, am, x.shape, k, s, p)
+    assert _rel_err(dx, xr.grad) < 1e-2
+
+
+def test_avgpool_relu():
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    x = _act(8, 512, 2, 2, dev)
+    assert _rel_err(nv.avgpool_fwd(x), x.float().mean((2, 3))) < 1e-2
+    dy = torch.randn(8, 512, device=dev).to(torch.bfloat16)
+    dx = nv.avgpool_bwd(dy, x.shape)
+    assert _rel_err(dx, (dy.float() / 4)[:, :, None, None].expand(8, 512, 2, 2)) < 1e-2
+    g = nv.relu_bwd(x, x)
+    assert torch.equal(g.float(), (x.float() * (x.float() > 0)))
+
+
+@pytest.mark.parametrize("B,C,dt", [(32, 1000, torch.bfloat16), (256, 10, torch.float32), (1000, 10, torch.bfloat16), (5, 16, torch.float32)])
+def test_softmax_xent(B, C, dt):
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    torch.manual_seed(3)
+    lg = (torch.randn(B, C, device=dev) * 3).to(dt)
+    t = torch.randint(0, min(C, 10), (B,), device=dev)
+    lr = lg.float().requires_grad_(True)
+    loss_r = F.cross_entropy(lr, t)
+    loss_r.backward()
+    for _ in range(2):       # twice: the ticket counter resets itself
+        loss, dl = nv.softmax_xent(lg, t, 1.0 / B)
+        assert abs(float(loss) - float(loss_r)) < 2e-3 * max(1.0, abs(float(loss_r)))
+        assert _rel_err(dl, lr.grad) < 1e-2
+
+
+def test_bce_and_eval_count():
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    x = torch.randn(64, device=dev)
+    t = (torch.rand(64, device=dev) > 0.5).float()
+    xr = x.clone().requires_grad_(True)
+    lr = F.binary_cross_entropy_with_logits(xr, t)
+    lr.backward()
+    loss, dl = nv.bce_logits(x, t, 1.0 / 64)
+    assert abs(float(loss) - float(lr)) < 1e-4 and _rel_err(dl, xr.grad) < 1e-4
+    lg = torch.randn(1000, 10, device=dev)
+    tg = torch.randint(0, 10, (1000,), device=dev)
+    correct = torch.zeros((), dtype=torch.int32, device=dev)
+    nll = torch.zeros((), device=dev)
+    nv.eval_count(lg, tg, correct, nll)
+    assert int(correct) == int((lg.argmax(1) == tg).sum())
+    assert abs(float(nll) - float(F.nll_loss(lg, tg, reduction="sum"))) < 1e-2
+
+
+def test_sgd_adam_flat():
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    torch.manual_seed(4)
+    n = 4096 * 3
+    p = torch.randn(n, device=dev)
+    pr = p.clone().requires_grad_(True)
+    m = torch.zeros(n, device=dev)
+    sh = torch.zeros(n, dtype=torch.bfloat16, device=dev)
+    opt = torch.optim.SGD([pr], lr=0.01, momentum=0.9, weight_decay=1e-4)
+    for _ in range(3):
+        g = torch.randn(n, device=dev)
+        pr.grad = g.clone()
+        opt.step()
+        gg = g.clone()
+        nv.sgd_step(p, gg, m, sh, 0.01, 0.9, 0.0, 1e-4, False, 1.0, True)
+        assert float(gg.abs().max()) == 0.0
+    assert torch.allclose(p, pr.detach(), atol=1e-5, rtol=1e-5)
+    assert torch.equal(sh, p.to(torch.bfloat16))
+    p = torch.randn(n, device=dev)
+    pr = p.clone().requires_grad_(True)
+    m, v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    step = torch.zeros((), dtype=torch.int32, device=dev)
+    opt = torch.optim.Adam([pr], lr=1e-3)
+    for _ in range(3):
+        g = torch.randn(n, device=dev)
+        pr.grad = g.clone()
+        opt.step()
+        nv.adam_step(p, g.clone(), m, v, None, 1e-3, 0.9, 0.999, 1e-8, 0.0, step, 1.0, False)
+    assert torch.allclose(p, pr.detach(), atol=1e-5, rtol=1e-4)
+
+
+def test_augment_and_trojan():
+    from b200ddp.ops import native as nv
+    from b200ddp.utils.data import CIFAR10_MEAN, CIFAR10_STD, augment_reference
+    dev = _dev()
+    torch.manual_seed(5)
+    img = torch.randint(0, 256, (16, 32, 32, 3), dtype=torch.uint8)
+    off = torch.stack([torch.randint(0, 9, (16,)), torch.randint(0, 9, (16,)), torch.randint(0, 2, (16,))], 1).to(torch.int32)
+    ref = augment_reference(img, offsets=off)
+    mean = torch.tensor(CIFAR10_MEAN, device=dev)
+    inv = 1.0 / torch.tensor(CIFAR10_STD, device=dev)
+    out = nv.augment(img.to(dev), off.to(dev), mean, inv, c_out=8)
+    assert out.shape == (16, 8, 32, 32) and float(out[:, 3:].abs().max()) == 0.0
+    assert torch.allclose(out[:, :3].float().cpu(), ref, atol=2e-2, rtol=1e-2)
+    out32 = nv.augment(img.to(dev), off.to(dev), mean, inv, nchw_fp32=True)
+    assert torch.allclose(out32.cpu(), ref, atol=1e-5)
+    x = torch.rand(6, 3, 32, 32, device=dev)
+    pat = torch.rand(3, 4, 4, device=dev)
+    mask = torch.tensor([1, 0, 1, 1, 0, 1], dtype=torch.uint8, device=dev)
+    xr = x.clone()
+    for i in range(6):
+        if mask[i]:
+            xr[i, :, 5:9, 7:11] = 0.3 * pat + 0.7 * xr[i, :, 5:9, 7:11]
+    nv.trojan_stamp_(x, pat, 5, 7, 0.3, mask)
+    assert torch.allclose(x, xr, atol=1e-6)
