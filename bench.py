@@ -1,0 +1,162 @@
+#!/usr/bin/env python
+"""Headline benchmark: images/sec of the workshop's GPU training job (BASELINE.json / BASELINE.md §1:
+torchvision-topology resnet18 with the 1000-way head on 32x32 CIFAR-10-shaped data, global batch 256
+divided by the world size as ``cifar10-distributed-smddp-gpu.py:123`` does, SGD lr 0.01 momentum 0.9).
+
+    python bench.py --gpus N --steps K --warmup W            # this framework (backend 'b200')
+    python bench.py --impl reference --gpus N ...            # unmodified reference, torch DDP + NCCL
+
+One full training step = GPU augmentation of the uint8 batch, forward, loss, backward with the fused
+NVLink gradient all-reduce, fused SGD.  Two numbers are reported:
+  value      device-timed steps (CUDA events around each CUDA-graph replay, L2 flushed between timed
+             iterations, max over ranks);
+  e2e.value  the same K steps through the public ``TrainStep.__call__`` API including, every step, the
+             H2D copy of that step's uint8 images/labels/crop offsets from pinned host memory and the
+             D2H read of the loss.
+Synthetic data, random-init weights (no network on the box).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+BASELINE_IMG_S = 4518.0   # BASELINE.md §1 *derived* lower bound: 750,000 img / 166 s on 8 x A100 (not a published figure)
+
+
+def run_own(args) -> dict:
+    import torch
+    import b200ddp as bd
+    from b200ddp.models import get_model
+    from b200ddp.nn import CrossEntropyLoss
+    from b200ddp.ops import _lib as L
+    from b200ddp.ops import optim as boptim
+    from b200ddp.runtime.engine import TrainStep
+    from b200ddp.utils.timers import ClockSampler
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    bd.init_process_group(backend="b200", rank=rank, world_size=world)
+    dev = bd.get_device()
+    torch.manual_seed(1)
+    per_rank = max(args.global_batch // world, 1)
+    hw = 224 if args.model == "resnet50" else 32
+    model = bd.DistributedDataParallel(get_model(args.model).to(dev))
+    opt = boptim.SGD(model.parameters(), lr=0.01, momentum=0.9)
+    step = TrainStep(model, CrossEntropyLoss(), opt, per_rank, image_shape=(hw, hw, 3), device=dev,
+                     graph=not args.no_graph, seed=rank)
+
+    # host-side synthetic dataset in pinned memory: (W + K + 1) distinct batches
+    nb = args.warmup + args.steps + 1
+    g = torch.Generator().manual_seed(100 + rank)
+    xs = torch.randint(0, 256, (nb, per_rank, hw, hw, 3), dtype=torch.uint8, generator=g).pin_memory()
+    ys = torch.randint(0, 10, (nb, per_rank), dtype=torch.int64, generator=g).pin_memory()
+
+    # ---- count this framework's kernel launches in one eager step (graph replays launch the same set)
+    model.train()
+    c0 = L.LAUNCHES[0]
+    step._body(xs[0].to(dev), ys[0].to(dev), step._draw_offsets(per_rank).to(dev))
+    launches_per_step = L.LAUNCHES[0] - c0
+    torch.cuda.synchronize()
+
+    for i in range(args.warmup):                     # warm-up (captures the graph on the first call)
+        step(xs[i], ys[i], need_loss=(i == args.warmup - 1))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)       # > 126 MB L2
+
+    # ---- (1) device-timed steps, L2 flushed between iterations (flush outside the event pair)
+    bd.barrier()
+    torch.cuda.synchronize()
+    evs = []
+    with ClockSampler(dev.index or 0) as clocks:
+        for i in range(args.steps):
+            j = args.warmup + i
+            step.static_x.copy_(xs[j], non_blocking=True) if step.cuda else None
+            step.static_y.copy_(ys[j], non_blocking=True)
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            if step._graph is not None:
+                step._graph.replay()
+            else:
+                step._body(step.static_x, step.static_y, step.static_off)
+            b.record()
+            evs.append((a, b))
+        torch.cuda.synchronize()
+        bd.barrier()
+        torch.cuda.synchronize()
+        dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+
+        # ---- (2) end to end through the public API: pinned H2D inputs + D2H loss every step
+        bd.barrier()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        last = None
+        for i in range(args.steps):
+            j = args.warmup + i
+            last = step(xs[j], ys[j], need_loss=True)
+        b.record()
+        torch.cuda.synchronize()
+        e2e_ms = a.elapsed_time(b)
+        bd.barrier()
+    dev_ms = bd.max_over_ranks(dev_ms)
+    e2e_ms = bd.max_over_ranks(e2e_ms)
+    comm = bd.get_comm()
+    if comm is not None:
+        comm.check_health()
+    algos = sorted(set(comm.launch_log)) if comm is not None else []
+    imgs = args.steps * per_rank * world
+    value = imgs / (dev_ms / 1e3)
+    out = {
+        "impl": "b200ddp", "metric": "images/sec", "value": value, "unit": "images/sec", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": value / BASELINE_IMG_S, "dtype": "bf16", "data": "synthetic",
+        "e2e": {"value": imgs / (e2e_ms / 1e3), "unit": "images/sec",
+                "h2d_bytes_per_step": per_rank * (hw * hw * 3 + 8 + 12), "d2h_bytes_per_step": 4,
+                "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": launches_per_step * args.steps,
+        "clocks": clocks.summary(),
+        "config": {"model": args.model + " (torchvision topology, 1000-way head, %dx%d input)" % (hw, hw),
+                   "global_batch": per_rank * world, "seq_len": None, "parallelism": "dp%d" % world,
+                   "per_gpu_batch": per_rank, "optimizer": "SGD lr=0.01 momentum=0.9", "cuda_graph": step._graph is not None,
+                   "l2": "256 MiB buffer written between timed iterations (outside the event pair)",
+                   "launches_per_step": launches_per_step, "allreduce_algos": algos, "final_loss": last,
+                   "baseline_note": "vs_baseline divides by 4518 img/s, BASELINE.md's derived 8xA100 job-log bound; the reference publishes no number"},
+    }
+    bd.destroy_process_group()
+    return out if rank == 0 else {}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", type=str, default="b200ddp", choices=["b200ddp", "reference"])
+    ap.add_argument("--model", type=str, default="resnet18", choices=["resnet18", "resnet50", "custom"])
+    ap.add_argument("--global-batch", type=int, default=256)
+    ap.add_argument("--no-graph", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        try:
+            from run_reference import run
+            out = run(args.gpus, args.steps, args.warmup, args.global_batch, args.model)
+        except Exception as e:    # the reference arm must never take the harness down
+            out = {"impl": "reference", "unavailable": "%s: %s" % (type(e).__name__, str(e)[:200])}
+        if out.get("rank", 0) == 0:
+            out.pop("rank", None)
+            print(json.dumps(out), flush=True)
+        return
+    out = run_own(args)
+    if out:
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -56,7 +56,11 @@ def lib() -> ctypes.CDLL:
     return L
 
 
+LAUNCHES = [0]          # native entry points that returned success (one kernel launch each, adam = 2)
+
+
 def check(rc: int, what: str = "") -> None:
+    LAUNCHES[0] += 1
     if rc != 0:
         msg = lib().b200_last_error().decode(errors="replace")
         raise NativeError("b200ddp native call %s failed (rc=%d): %s" % (what, rc, msg))

@@ -69,7 +69,9 @@ class TrainStep:
         loss = self.criterion(out, y)
         loss.backward()
         self.optimizer.step()
-        return loss
+        # detach: a live loss keeps last step's autograd graph (and its AccumulateGrad nodes, which are
+        # bound to the stream they were created on) alive, which breaks CUDA-graph capture
+        return loss.detach()
 
     # ------------------------------------------------------------------ graph capture
     def _capture(self):
@@ -78,13 +80,14 @@ class TrainStep:
         with torch.cuda.stream(s):
             for _ in range(self.warmup_iters):       # also runs one-time setup (func attributes, buffers)
                 loss = self._body(self.static_x, self.static_y, self.static_off)
-                self.static_loss.copy_(loss.detach())
+                self.static_loss.copy_(loss)
+        del loss
         torch.cuda.current_stream(self.device).wait_stream(s)
         torch.cuda.synchronize(self.device)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
             loss = self._body(self.static_x, self.static_y, self.static_off)
-            self.static_loss.copy_(loss.detach())
+            self.static_loss.copy_(loss)
         self._graph = g
         self.steps_done += self.warmup_iters       # warm-up iterations were real optimizer steps
 
