@@ -38,6 +38,20 @@ def scratch(device: torch.device) -> torch.Tensor:
     return t
 
 
+_CONV_SCRATCH = {}
+CONV_SCRATCH_BYTES = 64 << 20
+
+
+def conv_scratch(device: torch.device) -> torch.Tensor:
+    """Split-K scratch of the tensor-core conv/linear kernels (tile tickets + fp32 partial tiles)."""
+    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+    t = _CONV_SCRATCH.get(key)
+    if t is None:
+        t = torch.zeros(CONV_SCRATCH_BYTES, dtype=torch.uint8, device=device)
+        _CONV_SCRATCH[key] = t
+    return t
+
+
 def _cl_ok(x: torch.Tensor) -> bool:
     return x.dim() == 4 and x.is_contiguous(memory_format=CL)
 
@@ -70,8 +84,9 @@ def conv_fwd(x: torch.Tensor, w_krsc: torch.Tensor, bias: Optional[torch.Tensor]
     Ho, Wo = conv_out_hw(H, W, R, S, stride, pad)
     y = empty_act(N, K, Ho, Wo, x.device)
     g = _geom(N, H, W, C, K, R, S, stride, pad)
+    sc = conv_scratch(x.device)
     L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w_krsc), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
-                                  L.stream_ptr()), "conv_fwd")
+                                  L.ptr(sc), c_size_t(sc.numel()), L.stream_ptr()), "conv_fwd")
     return y
 
 
@@ -81,7 +96,9 @@ def conv_dgrad(dy: torch.Tensor, w_krsc: torch.Tensor, x_shape, stride: int, pad
     assert _cl_ok(dy)
     dx = empty_act(N, C, H, W, dy.device)
     g = _geom(N, H, W, C, K, R, S, stride, pad)
-    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.stream_ptr()), "conv_dgrad")
+    sc = conv_scratch(dy.device)
+    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.ptr(sc), c_size_t(sc.numel()),
+                                    L.stream_ptr()), "conv_dgrad")
     return dx
 
 
@@ -104,8 +121,9 @@ def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], r
     assert x.is_contiguous() and w.is_contiguous()
     y = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
     g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
+    sc = conv_scratch(x.device)
     L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
-                                  L.stream_ptr()), "linear_fwd")
+                                  L.ptr(sc), c_size_t(sc.numel()), L.stream_ptr()), "linear_fwd")
     return y
 
 
@@ -114,7 +132,9 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     K = w.shape[1]
     dx = torch.empty((M, K), dtype=torch.bfloat16, device=dy.device)
     g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
-    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w), L.ptr(dx), byref(g), L.stream_ptr()), "linear_dgrad")
+    sc = conv_scratch(dy.device)
+    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w), L.ptr(dx), byref(g), L.ptr(sc), c_size_t(sc.numel()),
+                                    L.stream_ptr()), "linear_dgrad")
     return dx
 
 

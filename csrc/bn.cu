@@ -56,11 +56,28 @@ __device__ __forceinline__ bool publish_and_elect(float tot, float* partial, uns
   return last;
 }
 
+// all 256 threads of the electing CTA: thread t sums the partials of slot (t & 127) over half the row
+// blocks (independent loads, unrolled), the halves meet in shared memory.  Result valid for t < 128.
 __device__ __forceinline__ float sum_partials(const float* partial) {
+  __shared__ float half_sum[2 * kGroup];
   const int RB = gridDim.x, cg = blockIdx.y;
-  float t = 0.f;
-  for (int rb = 0; rb < RB; ++rb) t += __ldcg(partial + ((size_t)cg * RB + rb) * (2 * kGroup) + threadIdx.x);
-  return t;
+  const int slot = threadIdx.x & (2 * kGroup - 1), half = threadIdx.x >> 7;
+  const int mid = (RB + 1) >> 1;
+  const int lo = half ? mid : 0, hi = half ? RB : mid;
+  const float* base = partial + (size_t)cg * RB * (2 * kGroup) + slot;
+  float t0 = 0.f, t1 = 0.f, t2 = 0.f, t3 = 0.f;
+  int rb = lo;
+  for (; rb + 4 <= hi; rb += 4) {
+    t0 += __ldcg(base + (size_t)(rb + 0) * (2 * kGroup));
+    t1 += __ldcg(base + (size_t)(rb + 1) * (2 * kGroup));
+    t2 += __ldcg(base + (size_t)(rb + 2) * (2 * kGroup));
+    t3 += __ldcg(base + (size_t)(rb + 3) * (2 * kGroup));
+  }
+  for (; rb < hi; ++rb) t0 += __ldcg(base + (size_t)rb * (2 * kGroup));
+  const float t = (t0 + t1) + (t2 + t3);
+  if (half) half_sum[slot] = t;
+  __syncthreads();
+  return half ? 0.f : t + half_sum[slot];
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -88,7 +105,10 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, size_t rows, int C, const f
   }
   const float tot = cta_reduce_rows(s, q, sm);
   if (!publish_and_elect(tot, partial, counters)) return;
-  if (threadIdx.x < 2 * kGroup) fin[threadIdx.x >> 6][threadIdx.x & 63] = sum_partials(partial);
+  {
+    const float t = sum_partials(partial);
+    if (threadIdx.x < 2 * kGroup) fin[threadIdx.x >> 6][threadIdx.x & 63] = t;
+  }
   __syncthreads();
   if (threadIdx.x < kGroup) {
     const int ch = blockIdx.y * kGroup + threadIdx.x;
@@ -184,8 +204,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   }
   const float tot = cta_reduce_rows(s, q, sm);
   if (!publish_and_elect(tot, partial, counters)) return;
+  const float t = sum_partials(partial);
   if (threadIdx.x < 2 * kGroup) {
-    const float t = sum_partials(partial);
     const int which = threadIdx.x >> 6, ch = blockIdx.y * kGroup + (threadIdx.x & 63);
     if (ch < C) {
       sums[which * C + ch] = t;
@@ -240,13 +260,22 @@ dim3 bn_grid(size_t rows, int C, int per_sm) {
   return dim3((unsigned)rb, (unsigned)cg, 1);
 }
 
+// Reductions: few, fat CTAs (>= 256 rows each, <= 128 row blocks) so the electing CTA's final sum is short.
+dim3 bn_reduce_grid(size_t rows, int C) {
+  const int cg = (C + kGroup - 1) / kGroup;
+  size_t rb = rows / 256;
+  if (rb > 128) rb = 128;
+  if (rb < 1) rb = 1;
+  return dim3((unsigned)rb, (unsigned)cg, 1);
+}
+
 }  // namespace
 
 // scratch layout: [counters: 1024 x u32][partials: CG * RB * 128 floats]
 static constexpr size_t kCounterBytes = 4096;
 
 extern "C" size_t b200_bn_scratch_bytes(size_t rows, int C) {
-  dim3 g = bn_grid(rows, C, 4);
+  dim3 g = bn_reduce_grid(rows, C);
   return kCounterBytes + (size_t)g.x * g.y * 2 * kGroup * sizeof(float);
 }
 
@@ -257,7 +286,7 @@ extern "C" int b200_bn_stats(const void* x_bf16, size_t rows, int C, const float
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
   B200_REQUIRE((C + kGroup - 1) / kGroup <= 1024, "too many channel groups");
   B200_REQUIRE(scratch_bytes >= b200_bn_scratch_bytes(rows, C), "scratch too small (b200_bn_scratch_bytes)");
-  dim3 g = bn_grid(rows, C, 4);
+  dim3 g = bn_reduce_grid(rows, C);
   bn_stats_kernel<<<g, kThreads, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)x_bf16, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var,
       (float*)((char*)scratch + kCounterBytes), (unsigned*)scratch);
@@ -296,7 +325,7 @@ extern "C" int b200_bn_bwd_reduce(const void* dy_bf16, const void* x_bf16, const
   B200_REQUIRE(!relu || y_bf16, "relu mask needs y");
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
   B200_REQUIRE(scratch_bytes >= b200_bn_scratch_bytes(rows, C), "scratch too small (b200_bn_scratch_bytes)");
-  dim3 g = bn_grid(rows, C, 4);
+  dim3 g = bn_reduce_grid(rows, C);
   cudaStream_t s = (cudaStream_t)stream;
   float* partial = (float*)((char*)scratch + kCounterBytes);
   unsigned* counters = (unsigned*)scratch;

@@ -17,35 +17,33 @@
 //          gradient arena (split-K over positions across CTAs; the arena is zeroed by the optimizer).
 //
 // CTA = 5 warps.  Warps 0-3 gather operand tiles with 16-byte cp.async (zero-fill implements padding,
-// stride holes and tile tails) into 128B-swizzled shared memory, a 4-stage ring guarded by mbarriers;
+// stride holes and tile tails) into 128B-swizzled shared memory, a 6-stage ring guarded by mbarriers;
 // warp 4 allocates TMEM and one elected lane issues tcgen05.mma (M=128, N=64/128, K=16 per instruction,
 // 4 per stage), tcgen05.commit releases ring slots; warps 0-3 then read the accumulator back with
 // tcgen05.ld (32x32b, one row per thread) and run the epilogue.
-#include "common.cuh"
+//
+// Small-problem machinery (the reference's resnet18 runs at 8x8 .. 1x1 spatial):
+//   * filter taps that can never touch a real pixel (e.g. 8 of the 9 taps of a 3x3 conv on a 1x1 map)
+//     are dropped from the K loop (FWD/DGRAD) or from the grid (WGRAD) — decided on the host;
+//   * FWD/DGRAD split K across CTAs when the tile grid cannot fill 148 SMs: every split writes its fp32
+//     partial into the tile's accumulator in scratch (red.add.v4.f32); the last CTA of a tile (ticket
+//     counter) reads the sum, re-zeroes the accumulator and ticket (self-resetting) and runs the epilogue.
+#include <algorithm>
+
+#include "tc_ptx.cuh"
+
+using namespace b200tc;
 
 namespace {
 
 constexpr int MODE_FWD = 0, MODE_DGRAD = 1, MODE_WGRAD = 2;
 constexpr int BM = 128;
 constexpr int BK = 64;                 // bf16 elements per k-block = one 128-byte swizzle row
-constexpr int STAGES = 4;
-constexpr int LAG = 2;                 // cp.async groups kept in flight behind the newest one
+constexpr int STAGES = 6;
+constexpr int LAG = 4;                 // cp.async groups kept in flight behind the newest one
 constexpr int PRODUCERS = 128;
 constexpr int THREADS = PRODUCERS + 32;
-
-struct FastDiv {
-  uint32_t d, magic, shift;
-};
-__host__ FastDiv make_fastdiv(uint32_t d) {
-  FastDiv f;
-  f.d = d;
-  uint32_t s = 0;
-  while ((1ull << s) < d) ++s;
-  f.shift = s;
-  f.magic = (uint32_t)((((1ull << 32) * ((1ull << s) - d)) / d) + 1);
-  return f;
-}
-__device__ __forceinline__ uint32_t fdiv(uint32_t x, const FastDiv& f) { return (__umulhi(x, f.magic) + x) >> f.shift; }
+constexpr size_t kSplitCounterBytes = 16384;   // 4096 tile tickets at the head of the split-K scratch
 
 struct ConvParams {
   const __nv_bfloat16* x;    // image-side tensor (FWD/WGRAD: input, DGRAD: unused)
@@ -53,105 +51,22 @@ struct ConvParams {
   const __nv_bfloat16* dy;   // output-side tensor (DGRAD/WGRAD)
   void* out;                 // FWD: y bf16 [M][Cout]; DGRAD: dx bf16 [M][Cin]; WGRAD: dw fp32 [Cout][R*S*Cin]
   const float* bias;         // FWD only, may be null
+  float* partials;           // split-K scratch (FWD/DGRAD), fp32 accumulators [tile][128][BN], zero between uses
+  unsigned* tickets;         // split-K tile tickets
   int N, H, W, C;            // input geometry (C = Cin)
   int Kc, R, S, stride, pad; // Kc = Cout
   int Ho, Wo;
   int relu;
   uint32_t gemm_m, gemm_n, gemm_k;   // per mode
-  uint32_t kblocks, kb_per_split;
-  FastDiv div_c, div_s, div_kc, div_wo, div_ho, div_w, div_h, div_rs;
+  uint32_t nvk;              // number of (virtual) k-blocks that are executed
+  uint32_t kb_per_split;     // virtual k-blocks per grid.z slice
+  uint32_t cpt;              // k-blocks per filter tap (0: no tap skipping, virtual == real)
+  uint32_t splits;
+  unsigned long long tapmask;  // bit t set: tap t can touch a real pixel somewhere in the tensor
+  uint8_t tap_list[64];      // the set bits of tapmask, ascending
+  FastDiv div_c, div_s, div_kc, div_wo, div_ho, div_w, div_h, div_cpt;
 };
 
-// ------------------------------------------------------------------------------------------------
-// PTX wrappers
-// ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("{\n\t.reg .b64 st;\n\tmbarrier.arrive.shared::cta.b64 st, [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  const uint32_t addr = smem_u32(bar);
-  uint32_t done = 0;
-  uint32_t spins = 0;
-  while (true) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(done)
-        : "r"(addr), "r"(parity)
-        : "memory");
-    if (done) break;
-    if (++spins > (1u << 26)) __trap();   // a broken pipeline must fault, never hang the GPU
-  }
-}
-__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
-  const int sz = valid ? 16 : 0;   // src-size 0 => 16 bytes of zeros (padding / tails)
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t cols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)), "r"(cols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
-}
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* v) {
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
-      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
-        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
-        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
-        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-      : "r"(taddr)
-      : "memory");
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-
-// Shared-memory matrix descriptor, SWIZZLE_128B, version 1 (Blackwell).  Addresses/offsets in 16-byte units.
-//   K-major : rows of 128 B, 8-row groups SBO=1024 B apart (LBO unused -> 1)
-//   MN-major: K rows of 128 B (64 MN elements), 8-row groups SBO=1024 B apart, 64-element MN groups LBO apart
-__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  uint64_t d = 0;
-  d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
-  d |= (uint64_t)1 << 46;   // version
-  d |= (uint64_t)2 << 61;   // SWIZZLE_128B
-  return d;
-}
-// Instruction descriptor for kind::f16: bf16 x bf16 -> fp32
-__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
-         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
-
-__device__ __forceinline__ uint32_t swz(uint32_t row, uint32_t chunk) { return row * 128u + ((chunk ^ (row & 7u)) << 4); }
-
-// ------------------------------------------------------------------------------------------------
 template <int MODE, int BN>
 struct Cfg {
   static constexpr bool A_MN = (MODE == MODE_WGRAD);
@@ -162,21 +77,37 @@ struct Cfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
 
+__device__ __forceinline__ uint32_t virt2kb(const ConvParams& p, uint32_t v) {
+  if (p.cpt == 0) return v;
+  const uint32_t q = fdiv(v, p.div_cpt);
+  return (uint32_t)p.tap_list[q] * p.cpt + (v - q * p.cpt);
+}
+
 template <int MODE, int BN>
-__global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const ConvParams p) {
+__global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_constant__ ConvParams p) {
   using C = Cfg<MODE, BN>;
+  const uint32_t m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+  if (MODE == MODE_WGRAD && p.cpt != 0) {
+    // N tile = columns (r,s,ci): drop tiles whose taps never see a real pixel (their dW is exactly 0)
+    const uint32_t t_lo = fdiv(n0, p.div_c);
+    const uint32_t n_hi = min(n0 + (uint32_t)BN, p.gemm_n) - 1;
+    const uint32_t t_hi = fdiv(n_hi, p.div_c);
+    bool any = false;
+    for (uint32_t t = t_lo; t <= t_hi; ++t) any = any || ((p.tapmask >> t) & 1ull);
+    if (!any) return;
+  }
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint32_t* last_flag = tmem_slot + 1;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const uint32_t m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
-  const uint32_t kb_begin = blockIdx.z * p.kb_per_split;
-  const uint32_t kb_end = min(p.kblocks, kb_begin + p.kb_per_split);
-  const uint32_t nkb = kb_end > kb_begin ? kb_end - kb_begin : 0;
+  const uint32_t v_begin = blockIdx.z * p.kb_per_split;
+  const uint32_t v_end = min(p.nvk, v_begin + p.kb_per_split);
+  const uint32_t nkb = v_end > v_begin ? v_end - v_begin : 0;
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -192,14 +123,13 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const ConvParams p)
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  if (nkb > 0) {
-    if (warp < 4) {
+  if (warp < 4) {
+    if (nkb > 0) {
       // =============================== PRODUCERS (cp.async gather) ===============================
       const uint32_t smem_base = smem_u32(smem);
-      // ---- per-thread A row info
-      // K-major A (FWD/DGRAD): thread owns chunk column jA = tid&7 of rows (tid>>3) + 16*i, i<8
-      // MN-major A (WGRAD): 16 chunks per K row: column cA = tid&15, rows (tid>>4) + 8*i, i<8
-      int a_n[8], a_h[8], a_w[8];   // FWD: (n, ho*st-pad, wo*st-pad); DGRAD: (n, h+pad, w+pad); -1 => row out of range
+      // K-major A (FWD/DGRAD): thread owns chunk column tid&7 of rows (tid>>3) + 16*i, i<8
+      // MN-major A (WGRAD): 16 chunks per K row: column tid&15, rows (tid>>4) + 8*i, i<8
+      int a_n[8], a_h[8], a_w[8];   // FWD: (n, ho*st-pad, wo*st-pad); DGRAD: (n, h+pad, w+pad); n=-1: row out of range
       if (MODE != MODE_WGRAD) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -223,7 +153,7 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const ConvParams p)
           }
         }
       }
-      // ---- per-thread B info for WGRAD: chunk column -> (r, s, ci) is fixed for the whole tile
+      // WGRAD B: chunk column -> (r, s, ci) is fixed for the whole tile
       int wb_r = 0, wb_s = 0, wb_c = 0;
       bool wb_ok = false;
       if (MODE == MODE_WGRAD) {
@@ -237,7 +167,7 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const ConvParams p)
       }
 
       for (uint32_t it = 0; it < nkb; ++it) {
-        const uint32_t kb = kb_begin + it;
+        const uint32_t kb = (MODE == MODE_WGRAD) ? (v_begin + it) : virt2kb(p, v_begin + it);
         const uint32_t stage = it % STAGES, ph = (it / STAGES) & 1;
         mbar_wait(&empty_bar[stage], ph ^ 1);
         const uint32_t sa = smem_base + stage * C::STAGE_BYTES, sb = sa + C::A_BYTES;
@@ -247,7 +177,6 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const ConvParams p)
           const uint32_t j = tid & 7;
           const uint32_t k = kb * BK + j * 8;
           const bool k_ok = k < p.gemm_k;
-          // k -> (tap, channel)
           const uint32_t cdim = (MODE == MODE_FWD) ? (uint32_t)p.C : (uint32_t)p.Kc;
           const uint32_t tap = fdiv(k, MODE == MODE_FWD ? p.div_c : p.div_kc);
           const int ch = (int)(k - tap * cdim);
@@ -265,7 +194,10 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const ConvParams p)
               const int hn = a_h[i] - r, wn = a_w[i] - s;   // = ho*stride, wo*stride
               int ho = hn, wo = wn;
               bool div_ok = hn >= 0 && wn >= 0;
-              if (p.stride != 1) {
+              if (p.stride == 2) {
+                ho = hn >> 1; wo = wn >> 1;
+                div_ok = div_ok && ((hn | wn) & 1) == 0;
+              } else if (p.stride != 1) {
                 ho = hn / p.stride; wo = wn / p.stride;
                 div_ok = div_ok && (ho * p.stride == hn) && (wo * p.stride == wn);
               }
@@ -351,16 +283,65 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const ConvParams p)
         const uint32_t first = nkb > LAG ? nkb - LAG : 0;
         for (uint32_t it = first; it < nkb; ++it) mbar_arrive(&full_bar[it % STAGES]);
       }
-
-      // =============================== EPILOGUE (TMEM -> registers -> global) ===============================
       mbar_wait(tmem_full, 0);
       tc_fence_after();
-      const uint32_t row = warp * 32 + lane;          // accumulator row == TMEM lane
-      const uint32_t m = m0 + row;
+    }
+
+    // =============================== EPILOGUE (TMEM -> registers -> global) ===============================
+    const uint32_t row = warp * 32 + lane;          // accumulator row == TMEM lane
+    const uint32_t m = m0 + row;
+    bool do_final = true;
+    if (MODE != MODE_WGRAD && p.splits > 1) {
+      // ---- split-K: add this CTA's fp32 partial into the tile accumulator (scratch, zero between uses),
+      // elect the last CTA of the tile
+      const uint32_t tile_id = blockIdx.y * gridDim.x + blockIdx.x;
+      float* mine = p.partials + (size_t)tile_id * (BM * BN) + (size_t)row * BN;
+      if (nkb > 0) {
+#pragma unroll 1
+        for (int cb = 0; cb < BN / 32; ++cb) {
+          uint32_t v[32];
+          tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + cb * 32, v);
+#pragma unroll
+          for (int q = 0; q < 8; ++q)
+            asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mine + cb * 32 + 4 * q),
+                         "f"(__uint_as_float(v[4 * q])), "f"(__uint_as_float(v[4 * q + 1])),
+                         "f"(__uint_as_float(v[4 * q + 2])), "f"(__uint_as_float(v[4 * q + 3]))
+                         : "memory");
+        }
+      }
+      __threadfence();
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (tid == 0) {
+        const unsigned ticket = atomicAdd(p.tickets + tile_id, 1u);
+        const unsigned last = (ticket == p.splits - 1) ? 1u : 0u;
+        if (last) p.tickets[tile_id] = 0u;     // self-resetting
+        *last_flag = last;
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      do_final = (*last_flag != 0u);
+      if (do_final) __threadfence();
+    }
+    if (do_final && (nkb > 0 || MODE != MODE_WGRAD)) {
 #pragma unroll 1
       for (int cb = 0; cb < BN / 32; ++cb) {
         uint32_t v[32];
-        tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + cb * 32, v);
+        if (MODE != MODE_WGRAD && p.splits > 1) {
+          const uint32_t tile_id = blockIdx.y * gridDim.x + blockIdx.x;
+          float4* src = reinterpret_cast<float4*>(p.partials + (size_t)tile_id * (BM * BN) + (size_t)row * BN + cb * 32);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            const float4 t = __ldcg(src + q);
+            v[4 * q] = __float_as_uint(t.x); v[4 * q + 1] = __float_as_uint(t.y);
+            v[4 * q + 2] = __float_as_uint(t.z); v[4 * q + 3] = __float_as_uint(t.w);
+          }
+#pragma unroll
+          for (int q = 0; q < 8; ++q) __stcg(src + q, make_float4(0.f, 0.f, 0.f, 0.f));   // ready for the next launch
+        } else if (nkb > 0) {
+          tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + cb * 32, v);
+        } else {
+#pragma unroll
+          for (int q = 0; q < 32; ++q) v[q] = 0u;
+        }
         const uint32_t nn0 = n0 + cb * 32;
         if (m < p.gemm_m) {
           if (MODE == MODE_WGRAD) {
@@ -398,25 +379,25 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const ConvParams p)
           }
         }
       }
-    } else if (lane == 0) {
-      // =============================== MMA ISSUER (one thread) ===============================
-      constexpr uint32_t idesc = make_idesc(BM, BN, C::A_MN ? 1 : 0, C::B_MN ? 1 : 0);
-      const uint32_t smem_base = smem_u32(smem);
-      for (uint32_t it = 0; it < nkb; ++it) {
-        const uint32_t stage = it % STAGES, ph = (it / STAGES) & 1;
-        mbar_wait(&full_bar[stage], ph);
-        tc_fence_after();
-        const uint32_t sa = smem_base + stage * C::STAGE_BYTES, sb = sa + C::A_BYTES;
+    }
+  } else if (lane == 0 && nkb > 0) {
+    // =============================== MMA ISSUER (one thread) ===============================
+    constexpr uint32_t idesc = make_idesc(BM, BN, C::A_MN ? 1 : 0, C::B_MN ? 1 : 0);
+    const uint32_t smem_base = smem_u32(smem);
+    for (uint32_t it = 0; it < nkb; ++it) {
+      const uint32_t stage = it % STAGES, ph = (it / STAGES) & 1;
+      mbar_wait(&full_bar[stage], ph);
+      tc_fence_after();
+      const uint32_t sa = smem_base + stage * C::STAGE_BYTES, sb = sa + C::A_BYTES;
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          // K-major: +32 B per K=16 inside the 128-B swizzle row.  MN-major: +2 row groups (2048 B).
-          const uint64_t da = C::A_MN ? make_desc(sa + k * 2048, BK * 128, 1024) : make_desc(sa + k * 32, 16, 1024);
-          const uint64_t db = C::B_MN ? make_desc(sb + k * 2048, BK * 128, 1024) : make_desc(sb + k * 32, 16, 1024);
-          umma_bf16(tmem_base, da, db, idesc, (it | (uint32_t)k) != 0 ? 1u : 0u);
-        }
-        umma_commit(&empty_bar[stage]);            // ring slot free once these MMAs retire
-        if (it + 1 == nkb) umma_commit(tmem_full);  // accumulator complete
+      for (int k = 0; k < BK / 16; ++k) {
+        // K-major: +32 B per K=16 inside the 128-B swizzle row.  MN-major: +2 row groups (2048 B).
+        const uint64_t da = C::A_MN ? make_desc(sa + k * 2048, BK * 128, 1024) : make_desc(sa + k * 32, 16, 1024);
+        const uint64_t db = C::B_MN ? make_desc(sb + k * 2048, BK * 128, 1024) : make_desc(sb + k * 32, 16, 1024);
+        umma_bf16(tmem_base, da, db, idesc, (it | (uint32_t)k) != 0 ? 1u : 0u);
       }
+      umma_commit(&empty_bar[stage]);            // ring slot free once these MMAs retire
+      if (it + 1 == nkb) umma_commit(tmem_full);  // accumulator complete
     }
   }
   tc_fence_before();
@@ -445,6 +426,7 @@ int fill_common(ConvParams& p, const b200_conv_geom* g) {
   B200_REQUIRE(g != nullptr, "null geometry");
   B200_REQUIRE(g->C % 8 == 0 && g->K % 8 == 0, "channel counts must be multiples of 8 (16-byte gathers)");
   B200_REQUIRE(g->stride >= 1 && g->R >= 1 && g->S >= 1 && g->N >= 1, "bad geometry");
+  memset(&p, 0, sizeof(p));
   p.N = g->N; p.H = g->H; p.W = g->W; p.C = g->C;
   p.Kc = g->K; p.R = g->R; p.S = g->S; p.stride = g->stride; p.pad = g->pad;
   p.Ho = (g->H + 2 * g->pad - g->R) / g->stride + 1;
@@ -453,37 +435,99 @@ int fill_common(ConvParams& p, const b200_conv_geom* g) {
   B200_REQUIRE((size_t)g->N * g->H * g->W < (1ull << 31) && (size_t)g->N * p.Ho * p.Wo < (1ull << 31), "tensor too large for 32-bit tile indices");
   p.div_c = make_fastdiv(p.C); p.div_s = make_fastdiv(p.S); p.div_kc = make_fastdiv(p.Kc);
   p.div_wo = make_fastdiv(p.Wo); p.div_ho = make_fastdiv(p.Ho);
-  p.div_w = make_fastdiv(p.W); p.div_h = make_fastdiv(p.H); p.div_rs = make_fastdiv(p.R * p.S);
-  p.relu = 0; p.bias = nullptr; p.x = nullptr; p.w = nullptr; p.dy = nullptr; p.out = nullptr;
+  p.div_w = make_fastdiv(p.W); p.div_h = make_fastdiv(p.H);
+  p.div_cpt = make_fastdiv(1);
+  p.splits = 1;
+  // ---- filter taps that can touch a real pixel.  The relation "input row h pairs with output row ho
+  // through tap r" (h = ho*stride - pad + r) is the same for fwd, dgrad and wgrad.
+  unsigned long long mask = 0;
+  if (p.R * p.S <= 64) {
+    for (int r = 0; r < p.R; ++r) {
+      bool r_ok = false;
+      for (int ho = 0; ho < p.Ho && !r_ok; ++ho) { const int h = ho * p.stride - p.pad + r; r_ok = h >= 0 && h < p.H; }
+      for (int s = 0; s < p.S; ++s) {
+        bool s_ok = false;
+        for (int wo = 0; wo < p.Wo && !s_ok; ++wo) { const int w = wo * p.stride - p.pad + s; s_ok = w >= 0 && w < p.W; }
+        if (r_ok && s_ok) mask |= 1ull << (r * p.S + s);
+      }
+    }
+  } else {
+    mask = ~0ull;
+  }
+  p.tapmask = mask;
+  int n = 0;
+  for (int t = 0; t < p.R * p.S && t < 64; ++t)
+    if ((mask >> t) & 1ull) p.tap_list[n++] = (uint8_t)t;
   return 0;
+}
+
+// K-loop plan for FWD/DGRAD: `cdim` = channels per tap along K
+void plan_k(ConvParams& p, uint32_t cdim) {
+  const uint32_t kblocks = (p.gemm_k + BK - 1) / BK;
+  int ntaps_valid = 0;
+  for (int t = 0; t < 64; ++t) ntaps_valid += (int)((p.tapmask >> t) & 1ull);
+  if (p.R * p.S <= 64 && cdim % BK == 0 && ntaps_valid < p.R * p.S && ntaps_valid > 0) {
+    p.cpt = cdim / BK;
+    p.div_cpt = make_fastdiv(p.cpt);
+    p.nvk = (uint32_t)ntaps_valid * p.cpt;
+  } else {
+    p.cpt = 0;
+    p.nvk = kblocks;
+  }
+  p.kb_per_split = p.nvk;
+}
+
+// split K so the grid covers the machine when the tile grid alone cannot (small M x N)
+void plan_splits(ConvParams& p, uint32_t tiles, uint32_t bn, void* scratch, size_t scratch_bytes) {
+  p.splits = 1;
+  const uint32_t sms = (uint32_t)b200_num_sms();
+  if (scratch == nullptr || tiles * 2 > sms || tiles > 4096 || p.nvk < 4) return;
+  uint32_t want = sms / tiles;                           // one wave: tiles * splits <= #SMs (1 CTA per SM)
+  const uint32_t by_k = p.nvk / 2;                       // >= 2 k-blocks per split
+  if (want > by_k) want = by_k;
+  if (want > 16) want = 16;
+  if (scratch_bytes < kSplitCounterBytes + (size_t)tiles * BM * bn * sizeof(float)) return;
+  if (want < 2) return;
+  p.kb_per_split = (p.nvk + want - 1) / want;
+  p.splits = (p.nvk + p.kb_per_split - 1) / p.kb_per_split;
+  if (p.splits < 2) { p.splits = 1; p.kb_per_split = p.nvk; return; }
+  p.tickets = reinterpret_cast<unsigned*>(scratch);
+  p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + kSplitCounterBytes);
 }
 
 }  // namespace
 
 extern "C" int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g,
-                             int relu, void* stream) {
+                             int relu, void* scratch, size_t scratch_bytes, void* stream) {
   ConvParams p;
   int rc = fill_common(p, g);
   if (rc) return rc;
   B200_REQUIRE(x && w && y, "null tensor");
   p.x = (const __nv_bfloat16*)x; p.w = (const __nv_bfloat16*)w; p.out = y; p.bias = bias; p.relu = relu;
   p.gemm_m = (uint32_t)p.N * p.Ho * p.Wo; p.gemm_n = p.Kc; p.gemm_k = (uint32_t)p.R * p.S * p.C;
-  p.kblocks = (p.gemm_k + BK - 1) / BK; p.kb_per_split = p.kblocks;
+  plan_k(p, p.C);
   const bool narrow = p.gemm_n <= 64;
-  dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + (narrow ? 64 : 128) - 1) / (narrow ? 64 : 128), 1);
+  const uint32_t bn = narrow ? 64 : 128;
+  dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, 1);
+  plan_splits(p, grid.x * grid.y, bn, scratch, scratch_bytes);
+  grid.z = p.splits;
   return narrow ? launch<MODE_FWD, 64>(p, grid, (cudaStream_t)stream) : launch<MODE_FWD, 128>(p, grid, (cudaStream_t)stream);
 }
 
-extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream) {
+extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* scratch,
+                               size_t scratch_bytes, void* stream) {
   ConvParams p;
   int rc = fill_common(p, g);
   if (rc) return rc;
   B200_REQUIRE(dy && w && dx, "null tensor");
   p.dy = (const __nv_bfloat16*)dy; p.w = (const __nv_bfloat16*)w; p.out = dx;
   p.gemm_m = (uint32_t)p.N * p.H * p.W; p.gemm_n = p.C; p.gemm_k = (uint32_t)p.R * p.S * p.Kc;
-  p.kblocks = (p.gemm_k + BK - 1) / BK; p.kb_per_split = p.kblocks;
+  plan_k(p, p.Kc);
   const bool narrow = p.gemm_n <= 64;
-  dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + (narrow ? 64 : 128) - 1) / (narrow ? 64 : 128), 1);
+  const uint32_t bn = narrow ? 64 : 128;
+  dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, 1);
+  plan_splits(p, grid.x * grid.y, bn, scratch, scratch_bytes);
+  grid.z = p.splits;
   return narrow ? launch<MODE_DGRAD, 64>(p, grid, (cudaStream_t)stream) : launch<MODE_DGRAD, 128>(p, grid, (cudaStream_t)stream);
 }
 
@@ -495,18 +539,37 @@ extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b
   B200_REQUIRE(x && dy && dw, "null tensor");
   p.x = (const __nv_bfloat16*)x; p.dy = (const __nv_bfloat16*)dy; p.out = dw;
   p.gemm_m = p.Kc; p.gemm_n = (uint32_t)p.R * p.S * p.C; p.gemm_k = (uint32_t)p.N * p.Ho * p.Wo;
-  p.kblocks = (p.gemm_k + BK - 1) / BK;
+  const uint32_t kblocks = (p.gemm_k + BK - 1) / BK;
+  p.nvk = kblocks;
+  int ntaps_valid = 0;
+  for (int t = 0; t < 64; ++t) ntaps_valid += (int)((p.tapmask >> t) & 1ull);
+  p.cpt = (p.R * p.S <= 64 && ntaps_valid < p.R * p.S) ? 1u : 0u;   // non-zero enables the N-tile skip; K is never remapped
   const bool narrow = p.gemm_n <= 64;
   const uint32_t bn = narrow ? 64 : 128;
-  const uint32_t tiles = ((p.gemm_m + BM - 1) / BM) * ((p.gemm_n + bn - 1) / bn);
-  // split the position reduction so the grid covers the machine ~2x; >= 4 k-blocks per CTA
+  uint32_t n_tiles = (p.gemm_n + bn - 1) / bn;
+  uint32_t live_n_tiles = n_tiles;
+  if (p.cpt) {   // only the live tiles count when sizing the split
+    live_n_tiles = 0;
+    for (uint32_t t = 0; t < n_tiles; ++t) {
+      const uint32_t lo = (t * bn) / p.C, hi = (std::min((t + 1) * bn, p.gemm_n) - 1) / p.C;
+      bool any = false;
+      for (uint32_t q = lo; q <= hi && q < 64; ++q) any = any || ((p.tapmask >> q) & 1ull);
+      live_n_tiles += any ? 1 : 0;
+    }
+    if (live_n_tiles == 0) return 0;
+  }
+  const uint32_t tiles = ((p.gemm_m + BM - 1) / BM) * live_n_tiles;
+  // split the position reduction so the grid covers the machine ~2x; >= 2 k-blocks per CTA
   uint32_t splits = (2u * (uint32_t)b200_num_sms() + tiles - 1) / tiles;
   if (max_splits > 0 && splits > (uint32_t)max_splits) splits = (uint32_t)max_splits;
-  const uint32_t max_by_k = (p.kblocks + 3) / 4;
+  const uint32_t max_by_k = (kblocks + 1) / 2;
   if (splits > max_by_k) splits = max_by_k;
   if (splits < 1) splits = 1;
-  p.kb_per_split = (p.kblocks + splits - 1) / splits;
-  splits = (p.kblocks + p.kb_per_split - 1) / p.kb_per_split;
-  dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, splits);
+  p.kb_per_split = (kblocks + splits - 1) / splits;
+  splits = (kblocks + p.kb_per_split - 1) / p.kb_per_split;
+  p.splits = 1;   // WGRAD reduces its splits with red.add, not through scratch
+  // virt2kb must be the identity for WGRAD even though cpt != 0
+  p.div_cpt = make_fastdiv(1);
+  dim3 grid((p.gemm_m + BM - 1) / BM, n_tiles, splits);
   return narrow ? launch<MODE_WGRAD, 64>(p, grid, (cudaStream_t)stream) : launch<MODE_WGRAD, 128>(p, grid, (cudaStream_t)stream);
 }

@@ -36,6 +36,9 @@ CONV_CASES = [
     (3, 16, 14, 14, 8, 5, 1, 0),
     (2, 32, 17, 13, 72, 3, 1, 1),
     (2, 64, 56, 56, 64, 3, 1, 1),
+    (8, 512, 2, 2, 512, 3, 1, 1),     # split-K with many splits
+    (256, 512, 1, 1, 512, 3, 1, 1),   # 8 of 9 taps dead: tap skipping + split-K
+    (64, 128, 4, 4, 256, 1, 2, 0),    # 1x1 stride 2: dgrad tiles with no live tap
 ]
 
 
