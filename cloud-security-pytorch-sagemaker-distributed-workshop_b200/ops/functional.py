@@ -18,6 +18,7 @@ import torch
 import torch.nn.functional as F
 
 from . import native as nv
+from . import streams
 
 CL = torch.channels_last
 
@@ -119,8 +120,9 @@ class _Conv2dFn(torch.autograd.Function):
             exact = (Cp == C and Kp == K)
             sink = getattr(weight, "_b200_sink", None)
             if exact and sink is not None:
-                nv.conv_wgrad_(sink.flat.view(K, R, S, C), x, dy, stride, pad)
-                sink.done()
+                with streams.forked(x.device, x, dy):        # off the dgrad critical path
+                    nv.conv_wgrad_(sink.flat.view(K, R, S, C), x, dy, stride, pad)
+                    sink.done()
             else:
                 tmp = torch.zeros((Kp, R, S, Cp), dtype=torch.float32, device=x.device)
                 nv.conv_wgrad_(tmp, x, dy, stride, pad)
@@ -131,13 +133,13 @@ class _Conv2dFn(torch.autograd.Function):
                     dw = None
         db = None
         if bias is not None and bias.requires_grad:
-            g = dy.float().sum(dim=(0, 2, 3))[:K]
             bsink = getattr(bias, "_b200_sink", None)
             if bsink is not None:
-                bsink.flat[:K].add_(g)
+                nv.colsum_accum_(bsink.flat, dy, K)
                 bsink.done()
             else:
-                db = g
+                db = torch.zeros(K, dtype=torch.float32, device=dy.device)
+                nv.colsum_accum_(db, dy, K)
         return dx, dw, db, None, None, None
 
 
@@ -176,8 +178,9 @@ class _LinearFn(torch.autograd.Function):
             sink = getattr(weight, "_b200_sink", None)
             exact = (Kp == K and Np == N and nhwc_from is None)
             if exact and sink is not None:
-                nv.linear_wgrad_(sink.flat.view(N, K), x, dy)
-                sink.done()
+                with streams.forked(x.device, x, dy):
+                    nv.linear_wgrad_(sink.flat.view(N, K), x, dy)
+                    sink.done()
             else:
                 tmp = torch.zeros((Np, Kp), dtype=torch.float32, device=x.device)
                 nv.linear_wgrad_(tmp, x, dy)
@@ -194,13 +197,13 @@ class _LinearFn(torch.autograd.Function):
                     dw = g
         db = None
         if bias is not None and bias.requires_grad:
-            g = dy.float().sum(dim=0)[:N]
             bsink = getattr(bias, "_b200_sink", None)
             if bsink is not None:
-                bsink.flat[:N].add_(g)
+                nv.colsum_accum_(bsink.flat, dy, N)
                 bsink.done()
             else:
-                db = g
+                db = torch.zeros(N, dtype=torch.float32, device=dy.device)
+                nv.colsum_accum_(db, dy, N)
         return dx, dw, db, None, None
 
 

@@ -232,6 +232,13 @@ def avgpool_bwd(dy: torch.Tensor, x_shape) -> torch.Tensor:
     return dx
 
 
+def colsum_accum_(out_f32: torch.Tensor, dy: torch.Tensor, c_valid: int) -> None:
+    """out[:c_valid] += column sums of dy ([rows, C] bf16 matrix or channels-last activation)."""
+    rows, C = _rows_c(dy)
+    L.check(L.lib().b200_colsum_accum(L.ptr(dy), c_size_t(rows), c_int(C), c_int(c_valid), L.ptr(out_f32), L.stream_ptr()),
+            "colsum_accum")
+
+
 def relu_bwd(dy: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
     dx = torch.empty_like(dy)
     L.check(L.lib().b200_relu_bwd(L.ptr(dy), L.ptr(y), L.ptr(dx), c_size_t(dy.numel()), L.stream_ptr()), "relu_bwd")

@@ -188,6 +188,9 @@ class DistributedDataParallel(nn.Module):
 
     def _finalize_backward(self):
         self._callback_queued = False
+        if self.device.type == "cuda":
+            from ..ops import streams
+            streams.join(self.device)      # wgrad kernels forked onto the aux stream
         self.reducer.finalize()
         if self.require_backward_grad_sync:
             self._accum_count = 0

@@ -240,6 +240,11 @@ class SymmComm:
             cur = torch.cuda.current_stream(self.device)
             self._ready_event.record(cur)
             self.comm_stream.wait_event(self._ready_event)
+            from ..ops import streams
+            for other in streams.producers(self.device):   # bucket members written on the other stream
+                ev = torch.cuda.Event()
+                ev.record(other)
+                self.comm_stream.wait_event(ev)
             self._launch_allreduce(offset_bytes, numel, dtype, scale, self.comm_stream, algo)
             self._overlap_dirty = True
         else:

@@ -93,7 +93,24 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, size_t rows, int C, const f
 #pragma unroll
   for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
   if (c < C) {
-    for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
+    const size_t step = (size_t)gridDim.x * kRL;
+    size_t r = (size_t)blockIdx.x * kRL + rl;
+    for (; r + 3 * step < rows; r += 4 * step) {       // 4 independent 16-byte loads in flight per thread
+      bf16x8 v4[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) v4[u] = ld_vec(x + (r + u * step) * C + c);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        float f[8];
+        bf16x8_to_float(v4[u], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          s[k] += f[k];
+          q[k] = fmaf(f[k], f[k], q[k]);
+        }
+      }
+    }
+    for (; r < rows; r += step) {
       float f[8];
       bf16x8_to_float(ld_vec(x + r * C + c), f);
 #pragma unroll
@@ -189,7 +206,31 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
       mean[k] = stat[c + k];
       rstd[k] = stat[C + c + k];
     }
-    for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
+    const size_t step = (size_t)gridDim.x * kRL;
+    size_t r = (size_t)blockIdx.x * kRL + rl;
+    for (; r + step < rows; r += 2 * step) {           // 2 rows x 3 tensors = 6 independent loads in flight
+      bf16x8 gv[2], xr[2], yr[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        gv[u] = ld_vec(dy + (r + u * step) * C + c);
+        xr[u] = ld_vec(x + (r + u * step) * C + c);
+        if (kRelu) yr[u] = ld_vec(y + (r + u * step) * C + c);
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        float g[8], xv[8], yv[8];
+        bf16x8_to_float(gv[u], g);
+        bf16x8_to_float(xr[u], xv);
+        if (kRelu) bf16x8_to_float(yr[u], yv);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const float gg = (kRelu && !(yv[k] > 0.f)) ? 0.f : g[k];
+          s[k] += gg;
+          q[k] = fmaf(gg, (xv[k] - mean[k]) * rstd[k], q[k]);
+        }
+      }
+    }
+    for (; r < rows; r += step) {
       float g[8], xv[8], yv[8];
       bf16x8_to_float(ld_vec(dy + r * C + c), g);
       bf16x8_to_float(ld_vec(x + r * C + c), xv);

@@ -194,6 +194,36 @@ trojan_stamp_kernel(float* __restrict__ x, int N, int C, int H, int W, const flo
   }
 }
 
+
+// dbias[c] += sum_rows dy[row][c]   (bias gradient of conv / linear layers; fp32 atomics into the arena)
+__global__ void __launch_bounds__(256)
+colsum_accum_kernel(const __nv_bfloat16* __restrict__ dy, size_t rows, int C, int c_valid, float* __restrict__ out) {
+  __shared__ float sm[32][64];
+  const int v = threadIdx.x & 7, rl = threadIdx.x >> 3;
+  const int c = blockIdx.y * 64 + v * 8;
+  float acc[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+  if (c < C) {
+    for (size_t r = (size_t)blockIdx.x * 32 + rl; r < rows; r += (size_t)gridDim.x * 32) {
+      float f[8];
+      bf16x8_to_float(*reinterpret_cast<const bf16x8*>(dy + r * C + c), f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) sm[rl][v * 8 + k] = acc[k];
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    float t = 0.f;
+#pragma unroll 8
+    for (int r = 0; r < 32; ++r) t += sm[r][threadIdx.x];
+    const int ch = blockIdx.y * 64 + threadIdx.x;
+    if (ch < c_valid) atomicAdd(out + ch, t);
+  }
+}
+
 }  // namespace
 
 extern "C" int b200_maxpool_fwd(const void* x, void* y, uint8_t* argmax, int N, int H, int W, int C, int k, int stride,
@@ -263,6 +293,18 @@ extern "C" int b200_trojan_stamp(float* x, int N, int C, int H, int W, const flo
   const size_t total = (size_t)N * pattern_channels * p_h * p_w;
   if (total == 0) return 0;
   trojan_stamp_kernel<<<b200_grid_for(total, 256, 8), 256, 0, (cudaStream_t)stream>>>(x, N, C, H, W, pattern, pattern_channels, p_h, p_w, loc_h, loc_w, alpha, mask);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int b200_colsum_accum(const void* dy_bf16, size_t rows, int C, int c_valid, float* out, void* stream) {
+  B200_REQUIRE(dy_bf16 && out && C % 8 == 0 && c_valid <= C, "bad argument");
+  if (rows == 0) return 0;
+  size_t rb = rows / 64;
+  if (rb < 1) rb = 1;
+  if (rb > 64) rb = 64;
+  dim3 grid((unsigned)rb, (unsigned)((C + 63) / 64), 1);
+  colsum_accum_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy_bf16, rows, C, c_valid, out);
   B200_CHECK_LAUNCH();
   return 0;
 }

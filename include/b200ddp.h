@@ -135,6 +135,8 @@ int b200_maxpool_bwd(const void* dy, const uint8_t* argmax, void* dx, int N, int
 int b200_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
 int b200_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
 int b200_relu_bwd(const void* dy, const void* y, void* dx, size_t n, void* stream);
+/* out[c] += sum over rows of dy[row][c] for c < c_valid (bias gradients; replaces ATen sum). */
+int b200_colsum_accum(const void* dy_bf16, size_t rows, int C, int c_valid, float* out, void* stream);
 /* layout 0: out = NHWC bf16 with C_out >= C channels (zero padded); layout 1: NCHW fp32.
  * offsets [N][3] int32 = (crop dy, crop dx in 0..2*pad, flip) or NULL for the identity crop. */
 int b200_augment(const uint8_t* img_u8, const int32_t* offsets, void* out, int N, int H, int W, int C,

@@ -1,0 +1,178 @@
+"""Whole-model checks on the GPU: native forward/backward against the same model evaluated with plain
+PyTorch fp32 on the CPU, the DDP flat-arena/optimizer path, and CUDA-graph vs eager training."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    return torch.device("cuda", 0)
+
+
+def _rel(a, b):
+    a, b = a.detach().float().cpu(), b.detach().float().cpu()
+    return float((a - b).norm() / (b.norm() + 1e-12))
+
+
+@pytest.fixture(scope="module")
+def pg():
+    import b200ddp as bd
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    if not bd.is_initialized():
+        bd.init_process_group(backend="b200", rank=0, world_size=1)
+    yield bd
+    bd.destroy_process_group()
+
+
+def out_classes(model):
+    return model.fc.out_features if hasattr(model, "fc") else 10
+
+
+class _RoundBF16(torch.autograd.Function):
+    """Straight-through bf16 rounding of a tensor and of its gradient: the rounding points of the native path."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.to(torch.bfloat16).float()
+
+
+def _bf16_oracle(model):
+    """Plain PyTorch fp32 model on the CPU with bf16 rounding inserted where the kernels round: layer
+    outputs (and their incoming gradients) and the weights of conv/linear layers."""
+    import torch.nn as nn
+    from b200ddp.nn import GlobalAvgPool
+    handles = []
+    for m in model.modules():
+        if isinstance(m, (nn.Conv2d, nn.Linear, nn.BatchNorm2d, GlobalAvgPool)):
+            handles.append(m.register_forward_hook(lambda mod, inp, out: _RoundBF16.apply(out)))
+        if isinstance(m, (nn.Conv2d, nn.Linear)):
+            m.weight.data = m.weight.data.to(torch.bfloat16).float()
+    return handles
+
+
+@pytest.mark.parametrize("name,batch,hw", [("custom", 64, 32), ("resnet18", 32, 64)])
+def test_model_fwd_bwd_matches_cpu_fp32(name, batch, hw):
+    """Oracle: the same model in plain PyTorch fp32 on the CPU with bf16 rounding at the kernels' rounding
+    points (tight tolerance); the un-rounded fp32 model is reported alongside (bf16 training noise)."""
+    from b200ddp.models import get_model
+    from b200ddp.ops import functional as BF
+    dev = _dev()
+    torch.manual_seed(0)
+    base = get_model(name)
+    for m in base.modules():            # weights exactly representable in bf16: one rounding point fewer to model
+        if isinstance(m, (torch.nn.Conv2d, torch.nn.Linear)):
+            m.weight.data = m.weight.data.to(torch.bfloat16).float()
+    gpu = copy.deepcopy(base).to(dev)
+    pure = copy.deepcopy(base)
+    ref = copy.deepcopy(base)
+    _bf16_oracle(ref)
+    # resnet18 at random init is badly conditioned in bf16: rounding the FORWARD activations alone moves the
+    # early-layer gradients by ~35% (BN backward cancels a large common mode; measured on the CPU with the
+    # oracle below, printed as 'noise').  The workshop Net matches its oracle to 4 decimals, every kernel is
+    # checked on its own in test_gpu_kernels.py, so resnet18 gets a bound of the size of that noise.
+    x = torch.randn(batch, 3, hw, hw).to(torch.bfloat16).float()
+    # labels over the whole logit range: with 10 labels on a 1000-way head every sample pushes the same 990
+    # logits down, BN backward cancels that common mode and what is left is dominated by rounding noise
+    y = torch.randint(0, out_classes(base), (batch,))
+    for m in (ref, pure, gpu):
+        m.train()
+    out_r = ref(x)
+    loss_r = F.cross_entropy(out_r, y)
+    loss_r.backward()
+    F.cross_entropy(pure(x), y).backward()
+    BF.assume_unit_loss_grad(False)
+    out_g = gpu(x.to(dev))
+    loss_g = BF.cross_entropy(out_g.contiguous(), y.to(dev))
+    loss_g.backward()
+    torch.cuda.synchronize()
+    assert _rel(out_g, out_r) < (8e-2 if name == "resnet18" else 2e-2)
+    assert abs(float(loss_g.detach()) - float(loss_r.detach())) < 1e-2 * max(1.0, abs(float(loss_r.detach())))
+    errs, noise = {}, {}
+    for (n, pr), (_, pp), (_, pg_) in zip(ref.named_parameters(), pure.named_parameters(), gpu.named_parameters()):
+        assert pg_.grad is not None, n
+        errs[n] = round(_rel(pg_.grad, pr.grad), 4)
+        noise[n] = round(_rel(pr.grad, pp.grad), 4)
+    print("grad rel error vs bf16-rounded oracle:", errs)
+    print("bf16 oracle vs un-rounded fp32 (inherent bf16 noise):", noise)
+    lim = 0.45 if name == "resnet18" else 0.02
+    bad = {k: v for k, v in errs.items() if v > lim}
+    assert not bad, (bad, errs)
+
+
+def test_ddp_world1_step_matches_torch_sgd(pg):
+    from b200ddp.models import get_model
+    from b200ddp.nn import CrossEntropyLoss
+    from b200ddp.ops import functional as BF
+    from b200ddp.ops import optim as boptim
+    dev = _dev()
+    torch.manual_seed(1)
+    ref = get_model("custom")
+    net = copy.deepcopy(ref).to(dev)
+    ddp = pg.DistributedDataParallel(net)
+    assert all(k.startswith("module.") for k in ddp.state_dict().keys())
+    opt = boptim.SGD(ddp.parameters(), lr=0.05, momentum=0.9)
+    opt_r = torch.optim.SGD(ref.parameters(), lr=0.05, momentum=0.9)
+    BF.assume_unit_loss_grad(False)
+    crit = CrossEntropyLoss()
+    x = torch.randn(64, 3, 32, 32)
+    y = torch.randint(0, 10, (64,))
+    for _ in range(3):
+        opt_r.zero_grad()
+        F.cross_entropy(ref(x), y).backward()
+        opt_r.step()
+        opt.zero_grad()
+        crit(ddp(x.to(dev)), y.to(dev)).backward()
+        opt.step()
+    torch.cuda.synchronize()
+    for (n, a), (_, b) in zip(ref.named_parameters(), net.named_parameters()):
+        assert _rel(b, a) < 2e-2, n
+    assert float(ddp.flat_grads.abs().max()) == 0.0          # zeroed by the fused step
+    sd = {k: v for k, v in net.state_dict().items()}
+    assert sd["conv1.weight"].shape == (6, 3, 5, 5)
+    # the bf16 shadow follows the fp32 masters
+    assert torch.equal(ddp.flat_shadow, ddp.flat_params.to(torch.bfloat16))
+
+
+def test_graph_step_matches_eager(pg):
+    from b200ddp.models import get_model
+    from b200ddp.nn import CrossEntropyLoss
+    from b200ddp.ops import optim as boptim
+    from b200ddp.runtime.engine import TrainStep
+    dev = _dev()
+    xs = torch.randint(0, 256, (6, 32, 32, 32, 3), dtype=torch.uint8).pin_memory()
+    ys = torch.randint(0, 10, (6, 32)).pin_memory()
+    losses = {}
+    for graph in (False, True):
+        torch.manual_seed(3)
+        net = pg.DistributedDataParallel(get_model("resnet18").to(dev))
+        opt = boptim.SGD(net.parameters(), lr=0.01, momentum=0.9)
+        step = TrainStep(net, CrossEntropyLoss(), opt, 32, device=dev, graph=graph, seed=5, augment=False, warmup_iters=3)
+        if not graph:          # the graph path warms up with 3 real steps on the first batch before capturing
+            for _ in range(3):
+                step(xs[0], ys[0])
+        losses[graph] = [step(xs[i], ys[i], need_loss=True) for i in range(6)]
+    for a, b in zip(losses[False], losses[True]):
+        assert abs(a - b) < 5e-2 * max(1.0, abs(a)), (losses[False], losses[True])
+    assert losses[True][-1] == losses[True][-1]
+
+
+def test_colsum_bias_grad():
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    dy = torch.randn(300, 88, device=dev).to(torch.bfloat16)
+    out = torch.ones(88, device=dev)
+    nv.colsum_accum_(out, dy, 84)
+    ref = 1.0 + dy.float().sum(0)
+    assert torch.allclose(out[:84], ref[:84], atol=1e-2, rtol=1e-3)
+    assert bool((out[84:] == 1.0).all())
