@@ -400,3 +400,69 @@ extern "C" int b200_bn_bwd_apply(const void* dy_bf16, const void* x_bf16, const 
   B200_CHECK_LAUNCH();
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// b200_bn_stats_noalloc — the same statistics pass for callers that cannot allocate device memory.
+//
+// Who that is: a host program that handed the whole GPU to its own memory pool at start-up (a later
+// cudaMalloc fails or fragments the pool), a latency-critical serving or real-time loop where cudaMalloc's
+// implicit device-wide synchronisation is not acceptable, and plain-C / non-torch runtimes binding this
+// library through the C ABI, which have no caching allocator to borrow a scratch buffer from.  For them the
+// reduction scratch (ticket counters + per-CTA partial sums) lives in the fixed array below instead of a
+// caller-provided buffer.  Inputs and outputs are still passed by the caller.
+//
+// Limits and rules
+//   * The array is B200_BN_NOALLOC_SCRATCH_BYTES (1 MiB) per GPU; every GPU that loads this library holds it
+//     until the process exits.  A problem whose b200_bn_scratch_bytes(rows, C) exceeds it is rejected with an
+//     error (rc < 0, text in b200_last_error()); 1 MiB covers up to ~2000 (row-block x channel-group) tiles,
+//     e.g. C <= 1024 at any row count.
+//   * The first call on each device resolves the array's device address (cudaGetSymbolAddress with that device
+//     current) and caches it.  Make that first call outside any stream capture.
+//   * This entry point calls no cudaMalloc/cudaFree and no allocating library routine.
+//   * All calls on a device share the one array and it keeps whatever the previous call left.  The ticket
+//     counters must start at zero, so every call clears them on `stream` before the kernel.  Two calls whose
+//     kernels overlap on the GPU (different streams, no dependency between them) race on the array: serialise
+//     them (same stream, or an event between them).
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_bn_noalloc_scratch[B200_BN_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+void* g_noalloc_ptr[kMaxDevices] = {nullptr};   // device address of g_bn_noalloc_scratch, per device ordinal
+}  // namespace
+
+extern "C" int b200_bn_stats_noalloc(const void* x_bf16, size_t rows, int C, const float* gamma, const float* beta,
+                                     float eps, float momentum, float* stat, float* running_mean,
+                                     float* running_var, void* stream) {
+  B200_REQUIRE(x_bf16 && gamma && beta && stat, "null argument");
+  B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
+  B200_REQUIRE((C + kGroup - 1) / kGroup <= 1024, "too many channel groups");
+  const size_t need = b200_bn_scratch_bytes(rows, C);
+  if (need > (size_t)B200_BN_NOALLOC_SCRATCH_BYTES) {
+    b200_set_error("b200_bn_stats_noalloc: rows=%zu C=%d needs %zu bytes of scratch, the built-in array holds %zu; "
+                   "use b200_bn_stats with a caller-provided buffer",
+                   rows, C, need, (size_t)B200_BN_NOALLOC_SCRATCH_BYTES);
+    return B200_ERR_ARG;
+  }
+  int dev = -1;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < kMaxDevices, "device ordinal out of range");
+  if (g_noalloc_ptr[dev] == nullptr) {
+    // In host code the array's name is only a handle: its device address has to be asked for, once per
+    // device, with that device current.
+    void* p = nullptr;
+    B200_CHECK_CUDA(cudaGetSymbolAddress(&p, g_bn_noalloc_scratch));
+    B200_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[dev] = p;
+  }
+  unsigned char* scratch = static_cast<unsigned char*>(g_noalloc_ptr[dev]);
+  cudaStream_t s = (cudaStream_t)stream;
+  // the tickets must be zero when the kernel starts; whatever an earlier (possibly aborted) call left goes
+  B200_CHECK_CUDA(cudaMemsetAsync(scratch, 0, kCounterBytes, s));
+  dim3 g = bn_reduce_grid(rows, C);
+  bn_stats_kernel<<<g, kThreads, 0, s>>>((const __nv_bfloat16*)x_bf16, rows, C, gamma, beta, eps, momentum, stat,
+                                         running_mean, running_var, (float*)(scratch + kCounterBytes),
+                                         (unsigned*)scratch);
+  B200_CHECK_LAUNCH();
+  return 0;
+}

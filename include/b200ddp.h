@@ -116,6 +116,19 @@ size_t b200_bn_scratch_bytes(size_t rows, int C);
 int b200_bn_stats(const void* x_bf16, size_t rows, int C, const float* gamma, const float* beta, float eps,
                   float momentum, float* stat, float* running_mean, float* running_var, void* scratch,
                   size_t scratch_bytes, void* stream);
+/* No counterpart in the reference (it has no native code, and no allocation-free calling convention).
+ * Same result as b200_bn_stats, for callers that cannot allocate device memory — a process whose own pool
+ * already owns the whole GPU, a serving / real-time loop that cannot take cudaMalloc's device-wide
+ * synchronisation, a plain-C runtime with no caching allocator to lend a buffer.  The scratch is a fixed
+ * B200_BN_NOALLOC_SCRATCH_BYTES array inside the library (held by every GPU that loads it, until exit);
+ * problems whose b200_bn_scratch_bytes(rows, C) exceed it are rejected with an error.  The first call on a
+ * device looks the array's address up (cudaGetSymbolAddress): make it before any stream capture.  No
+ * cudaMalloc/cudaFree, no allocating library call.  Calls share the array and clear its ticket counters on
+ * `stream` first; calls that overlap on the GPU race — keep them on one stream or order them with an event. */
+#define B200_BN_NOALLOC_SCRATCH_BYTES (1u << 20)
+int b200_bn_stats_noalloc(const void* x_bf16, size_t rows, int C, const float* gamma, const float* beta,
+                          float eps, float momentum, float* stat, float* running_mean, float* running_var,
+                          void* stream);
 int b200_bn_eval_prep(const float* gamma, const float* beta, const float* running_mean,
                       const float* running_var, float eps, float* stat, int C, void* stream);
 int b200_bn_apply(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C,
