@@ -42,8 +42,13 @@ _CONV_SCRATCH = {}
 CONV_SCRATCH_BYTES = 64 << 20
 
 
-def conv_scratch(device: torch.device) -> torch.Tensor:
+SPLIT_K = [__import__("os").environ.get("B200DDP_CONV_SPLITK", "1") not in ("0", "false", "off")]
+
+
+def conv_scratch(device: torch.device) -> Optional[torch.Tensor]:
     """Split-K scratch of the tensor-core conv/linear kernels (tile tickets + fp32 partial tiles)."""
+    if not SPLIT_K[0]:
+        return None
     key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
     t = _CONV_SCRATCH.get(key)
     if t is None:
@@ -86,7 +91,7 @@ def conv_fwd(x: torch.Tensor, w_krsc: torch.Tensor, bias: Optional[torch.Tensor]
     g = _geom(N, H, W, C, K, R, S, stride, pad)
     sc = conv_scratch(x.device)
     L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w_krsc), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
-                                  L.ptr(sc), c_size_t(sc.numel()), L.stream_ptr()), "conv_fwd")
+                                  L.ptr(sc), c_size_t(sc.numel() if sc is not None else 0), L.stream_ptr()), "conv_fwd")
     return y
 
 
@@ -97,7 +102,7 @@ def conv_dgrad(dy: torch.Tensor, w_krsc: torch.Tensor, x_shape, stride: int, pad
     dx = empty_act(N, C, H, W, dy.device)
     g = _geom(N, H, W, C, K, R, S, stride, pad)
     sc = conv_scratch(dy.device)
-    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.ptr(sc), c_size_t(sc.numel()),
+    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.ptr(sc), c_size_t(sc.numel() if sc is not None else 0),
                                     L.stream_ptr()), "conv_dgrad")
     return dx
 
@@ -123,7 +128,7 @@ def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], r
     g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
     sc = conv_scratch(x.device)
     L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
-                                  L.ptr(sc), c_size_t(sc.numel()), L.stream_ptr()), "linear_fwd")
+                                  L.ptr(sc), c_size_t(sc.numel() if sc is not None else 0), L.stream_ptr()), "linear_fwd")
     return y
 
 
@@ -133,7 +138,7 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     dx = torch.empty((M, K), dtype=torch.bfloat16, device=dy.device)
     g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
     sc = conv_scratch(dy.device)
-    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w), L.ptr(dx), byref(g), L.ptr(sc), c_size_t(sc.numel()),
+    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w), L.ptr(dx), byref(g), L.ptr(sc), c_size_t(sc.numel() if sc is not None else 0),
                                     L.stream_ptr()), "linear_dgrad")
     return dx
 

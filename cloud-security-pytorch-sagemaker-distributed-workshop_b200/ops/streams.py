@@ -9,13 +9,14 @@ branches).  ``join`` makes the current stream wait for everything forked so far.
 from __future__ import annotations
 
 import contextlib
+import os
 
 import torch
 
 _AUX = {}
 _DIRTY = {}
 _MAIN = {}
-ENABLED = [True]
+ENABLED = [os.environ.get("B200DDP_AUX_STREAM", "1") not in ("0", "false", "off")]
 
 
 def _key(device):

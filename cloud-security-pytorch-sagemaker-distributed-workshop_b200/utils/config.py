@@ -139,6 +139,6 @@ class CommConfig:
     oneshot_max_bytes: int = env_int("B200DDP_ONESHOT_MAX_BYTES", 64 * 1024)
     nvls_min_bytes: int = env_int("B200DDP_NVLS_MIN_BYTES", 64 * 1024)
     use_nvls: bool = env_flag("B200DDP_NVLS", True)
-    max_ctas: int = env_int("B200DDP_COMM_CTAS", 32)
+    max_ctas: int = env_int("B200DDP_COMM_CTAS", 64)
     spin_timeout_ms: int = env_int("B200DDP_SPIN_TIMEOUT_MS", 20000)
     debug: bool = os.environ.get("B200DDP_DEBUG", "").upper() in ("INFO", "1", "TRACE")

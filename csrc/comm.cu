@@ -294,7 +294,7 @@ int launch_world(const b200_comm& c, size_t offset, size_t chunks, float scale, 
     int blocks = clamp_blocks(chunks, U, max_blocks);
     allreduce_oneshot_kernel<DT, WORLD, U><<<blocks, kThreads, 0, s>>>(c, offset, c.peer[c.rank] + offset, chunks, scale, 1);
   } else if (algo == B200_ALGO_NVLS) {
-    constexpr int U = 4;
+    constexpr int U = 8;   // 8 x 16 B multimem.ld_reduce in flight per thread: the switch round trip is ~3 us
     int blocks = clamp_blocks((chunks + WORLD - 1) / WORLD, U, max_blocks);
     allreduce_shard_kernel<DT, WORLD, U, true><<<blocks, kThreads, 0, s>>>(c, offset, chunks, scale);
   } else {

@@ -55,7 +55,7 @@ def main():
     for dtype in (torch.float32, torch.bfloat16):
         es = 4 if dtype == torch.float32 else 2
         view = arena_f32.view(torch.uint8).view(dtype)
-        for nbytes in (16, 1024, 4096 + 16, 248 * 1024 + 32, 2052000 // 16 * 16, 8 << 20):
+        for nbytes in (16, 1024, 4096 + 16, 248 * 1024 + 32, 2052000 // 16 * 16, 8 << 20, 15853824, 28852224):
             n = nbytes // es
             exp, mine = expected_sum(n, world, dtype, nbytes % 9973)
             for algo in algos:
