@@ -94,10 +94,15 @@ class DistributedDataParallel(nn.Module):
         if self.device.type == "cuda" and shadow_dtype is not None:
             self.flat_shadow = torch.zeros(total, dtype=shadow_dtype, device=self.device)
 
+        # channels-last physical storage only for the weights of this package's conv modules on a GPU: a
+        # stock nn.Conv2d fed channels-last weights would hand channels-last activations to user code
+        # (the reference's `x.view(-1, 400)` then fails)
+        from ..nn.modules import Conv2d as _NativeConv
+        native_conv_w = {id(m.weight) for m in module.modules() if isinstance(m, _NativeConv)}
         with torch.no_grad():
             for i, p in enumerate(self.params):
                 off, n = offsets[i], p.numel()
-                cl = _is_conv_weight(p)
+                cl = _is_conv_weight(p) and id(p) in native_conv_w and self.device.type == "cuda"
                 src = p.detach()
                 if cl:   # channels-last physical layout, torch-shaped logical view
                     co, ci, r, s = p.shape

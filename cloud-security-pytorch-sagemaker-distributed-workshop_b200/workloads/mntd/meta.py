@@ -1,0 +1,183 @@
+"""MNTD meta-classifier: learnable query set -> shadow-model logits -> 2-layer MLP -> trojan score.
+
+Counterpart of ``notebooks/code/meta_classifier.py`` (``MetaClassifier`` :6-31, ``MetaClassifierOC`` :34-69)
+and ``notebooks/code/utils_meta.py`` (``load_model_setting`` :5-35, ``epoch_meta_train`` :38-72,
+``epoch_meta_eval`` :74-104, ``epoch_meta_train_oc`` :107-128, ``epoch_meta_eval_oc`` :130-150).
+
+Kept: one shadow model per optimisation step, gradients flowing through the shadow model into the queries,
+BCE-with-logits / hinge+L2 losses, AUC + (median-)threshold accuracy, ``basic_model.train()`` during
+meta-evaluation (the reference does that; it keeps dropout active).
+Changed: the reference re-reads one checkpoint file from disk per step (``torch.load(x)``, :49) — here a
+``ShadowBank`` loads every checkpoint once (``weights_only=True``: they come from an untrusted tree) and keeps
+the state dicts on the training device; ``np.asscalar`` (removed from numpy) is replaced.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from ...models.mntd.models import MODELS
+
+
+def load_model_setting(task: str):
+    """-> (Model, input_size, class_num, normed_mean, normed_std, is_discrete)  (utils_meta.py:5-35)."""
+    if task == "mnist":
+        return MODELS[task], (1, 28, 28), 10, np.array((0.1307,)), np.array((0.3081,)), False
+    if task == "cifar10":
+        return (MODELS[task], (3, 32, 32), 10, np.reshape(np.array((0.4914, 0.4822, 0.4465)), (3, 1, 1)),
+                np.reshape(np.array((0.247, 0.243, 0.261)), (3, 1, 1)), False)
+    if task == "audio":
+        return MODELS[task], (16000,), 10, None, None, False
+    if task == "rtNLP":
+        return MODELS[task], (1, 10, 300), 1, None, None, True
+    raise NotImplementedError("Unknown task %s" % task)
+
+
+class MetaClassifier(nn.Module):
+    def __init__(self, input_size, class_num, N_in=10, gpu=False):
+        super().__init__()
+        self.input_size, self.class_num, self.N_in, self.N_h = input_size, class_num, N_in, 20
+        self.inp = nn.Parameter(torch.zeros(self.N_in, *input_size).normal_() * 1e-3)
+        self.fc = nn.Linear(self.N_in * self.class_num, self.N_h)
+        self.output = nn.Linear(self.N_h, 1)
+        self.gpu = gpu
+        if gpu:
+            self.cuda()
+
+    def forward(self, pred):
+        emb = F.relu(self.fc(pred.reshape(self.N_in * self.class_num).to(self.fc.weight.dtype)))
+        return self.output(emb)
+
+    def loss(self, score, y):
+        y_var = torch.tensor([float(y)], device=score.device)
+        return F.binary_cross_entropy_with_logits(score, y_var)
+
+
+class MetaClassifierOC(nn.Module):
+    """One-class (SVDD/OC-SVM style) variant: hinge on a learned radius + L2 (meta_classifier.py:34-69)."""
+
+    def __init__(self, input_size, class_num, N_in=10, gpu=False):
+        super().__init__()
+        self.N_in, self.N_h, self.v = N_in, 20, 0.1
+        self.input_size, self.class_num = input_size, class_num
+        self.inp = nn.Parameter(torch.zeros(self.N_in, *input_size).normal_() * 1e-3)
+        self.fc = nn.Linear(self.N_in * self.class_num, self.N_h)
+        self.w = nn.Parameter(torch.zeros(self.N_h).normal_() * 1e-3)
+        self.r = 1.0
+        self.gpu = gpu
+        if gpu:
+            self.cuda()
+
+    def forward(self, pred, ret_feature=False):
+        emb = F.relu(self.fc(pred.reshape(self.N_in * self.class_num).to(self.fc.weight.dtype)))
+        return emb if ret_feature else torch.dot(emb, self.w)
+
+    def loss(self, score):
+        reg = (self.w ** 2).sum() / 2
+        for p in self.fc.parameters():
+            reg = reg + (p ** 2).sum() / 2
+        return reg + F.relu(self.r - score) / self.v - self.r
+
+    def update_r(self, scores):
+        self.r = float(np.percentile(scores, 100 * self.v))
+
+
+class ShadowBank:
+    """All shadow/target checkpoints of an experiment, loaded once and kept on ``device``."""
+
+    def __init__(self, paths: Sequence[str], device="cpu"):
+        self.device = torch.device(device)
+        self.states: Dict[str, Dict[str, torch.Tensor]] = {}
+        for p in paths:
+            if p not in self.states:
+                sd = torch.load(p, map_location="cpu", weights_only=True)
+                sd = {(k[7:] if k.startswith("module.") else k): v.to(self.device) for k, v in sd.items()}
+                self.states[p] = sd
+
+    def load_into(self, model: nn.Module, path: str):
+        model.load_state_dict(self.states[path] if path in self.states else
+                              torch.load(path, map_location=self.device, weights_only=True))
+
+
+def _score(meta_model, basic_model, is_discrete):
+    out = basic_model.emb_forward(meta_model.inp) if is_discrete else basic_model.forward(meta_model.inp)
+    return meta_model.forward(out)
+
+
+def _auc_acc(preds, labs, threshold):
+    from sklearn.metrics import roc_auc_score
+    preds, labs = np.array(preds), np.array(labs)
+    auc = roc_auc_score(labs, preds) if len(set(labs.tolist())) > 1 else float("nan")
+    if threshold == "half":
+        threshold = float(np.median(preds))
+    return auc, float(((preds > threshold) == labs).mean())
+
+
+def epoch_meta_train(meta_model, basic_model, optimizer, dataset: List[Tuple[str, int]], is_discrete, threshold=0.0,
+                     bank: ShadowBank = None):
+    meta_model.train()
+    basic_model.train()
+    bank = bank or ShadowBank([x for x, _ in dataset], next(meta_model.parameters()).device)
+    cum_loss, preds, labs = 0.0, [], []
+    for i in np.random.permutation(len(dataset)):
+        x, y = dataset[i]
+        bank.load_into(basic_model, x)
+        score = _score(meta_model, basic_model, is_discrete)
+        l = meta_model.loss(score, y)
+        optimizer.zero_grad()
+        l.backward()
+        optimizer.step()
+        cum_loss += float(l.item())
+        preds.append(float(score.item()))
+        labs.append(y)
+    auc, acc = _auc_acc(preds, labs, threshold)
+    return cum_loss / len(dataset), auc, acc
+
+
+def epoch_meta_eval(meta_model, basic_model, dataset, is_discrete, threshold=0.0, bank: ShadowBank = None):
+    meta_model.eval()
+    basic_model.train()                      # as in the reference (utils_meta.py:76)
+    bank = bank or ShadowBank([x for x, _ in dataset], next(meta_model.parameters()).device)
+    cum_loss, preds, labs = 0.0, [], []
+    with torch.no_grad():
+        for x, y in dataset:
+            bank.load_into(basic_model, x)
+            score = _score(meta_model, basic_model, is_discrete)
+            cum_loss += float(meta_model.loss(score, y).item())
+            preds.append(float(score.item()))
+            labs.append(y)
+    auc, acc = _auc_acc(preds, labs, threshold)
+    return cum_loss / len(preds), auc, acc
+
+
+def epoch_meta_train_oc(meta_model, basic_model, optimizer, dataset, is_discrete, bank: ShadowBank = None):
+    bank = bank or ShadowBank([x for x, _ in dataset], next(meta_model.parameters()).device)
+    scores, cum_loss = [], 0.0
+    for i in np.random.permutation(len(dataset)):
+        x, y = dataset[i]
+        assert y == 1
+        bank.load_into(basic_model, x)
+        score = _score(meta_model, basic_model, is_discrete)
+        scores.append(float(score.item()))
+        loss = meta_model.loss(score)
+        optimizer.zero_grad()
+        loss.backward()
+        optimizer.step()
+        cum_loss += float(loss.item())
+        meta_model.update_r(scores)
+    return cum_loss / len(dataset)
+
+
+def epoch_meta_eval_oc(meta_model, basic_model, dataset, is_discrete, threshold=0.0, bank: ShadowBank = None):
+    bank = bank or ShadowBank([x for x, _ in dataset], next(meta_model.parameters()).device)
+    preds, labs = [], []
+    with torch.no_grad():
+        for x, y in dataset:
+            bank.load_into(basic_model, x)
+            preds.append(float(_score(meta_model, basic_model, is_discrete).item()))
+            labs.append(y)
+    return _auc_acc(preds, labs, threshold)

@@ -1,0 +1,189 @@
+"""CPU tier (no GPU): entry-point contract, data sharding, bucket layout, models, checkpoints."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_CODE = "/root/reference/notebooks/code"
+
+
+# ------------------------------------------------------------------ config / env contract
+def test_parse_args_reference_flags(monkeypatch):
+    from b200ddp.utils.config import parse_args
+    monkeypatch.setenv("SM_HOSTS", '["algo-1","algo-2"]')
+    monkeypatch.setenv("SM_CURRENT_HOST", "algo-2")
+    monkeypatch.setenv("SM_MODEL_DIR", "/tmp/m")
+    monkeypatch.setenv("SM_CHANNEL_TRAIN", "/tmp/d")
+    cfg = parse_args(["--model-type", "custom", "--batch-size", "64", "--epochs", "20", "--lr", "0.01",
+                      "--momentum", "0.9", "--backend", "gloo", "--test-batch-size", "500", "--log-interval", "7"])
+    assert (cfg.model_type, cfg.batch_size, cfg.epochs, cfg.lr, cfg.momentum) == ("custom", 64, 20, 0.01, 0.9)
+    assert cfg.backend == "gloo" and cfg.test_batch_size == 500 and cfg.log_interval == 7
+    assert cfg.model_dir == "/tmp/m" and cfg.data_dir == "/tmp/d"
+
+
+def test_defaults_without_sagemaker_env(monkeypatch):
+    from b200ddp.utils.config import parse_args
+    for k in ("SM_HOSTS", "SM_CURRENT_HOST", "SM_MODEL_DIR", "SM_CHANNEL_TRAIN"):
+        monkeypatch.delenv(k, raising=False)
+    cfg = parse_args([])                 # the reference raises KeyError here
+    assert cfg.hosts == ["algo-1"] and cfg.current_host == "algo-1" and cfg.momentum == 0.5 and cfg.seed == 1
+    assert parse_args(["--hosts", "a,b"]).hosts == ["a", "b"]            # not split into characters
+    assert parse_args(["--hosts", '["x","y","z"]']).hosts == ["x", "y", "z"]
+
+
+def test_log_line_formats():
+    from b200ddp.utils.logging import fmt_shard_line, fmt_test_line, fmt_train_line
+    assert fmt_train_line(1, 3200, 6250, 51.0, 1.639701) == "Train Epoch: 1 [3200/6250 (51%)] Loss: 1.639701"
+    assert fmt_test_line(-20.7798, 0.43) == "Test set: Average loss: -20.7798, Accuracy: 0.43\n"
+    assert fmt_shard_line(6250, 50000, "train") == "Processes 6250/50000 (12%) of train data"
+
+
+# ------------------------------------------------------------------ data
+@pytest.mark.parametrize("n,world", [(50000, 8), (1003, 4), (10, 3)])
+def test_shard_sampler_matches_torch_distributed_sampler(n, world):
+    from torch.utils.data.distributed import DistributedSampler
+    from b200ddp.utils.data import ShardSampler
+    ds = list(range(n))
+    for rank in range(world):
+        ref = list(DistributedSampler(ds, num_replicas=world, rank=rank, shuffle=True, seed=0))
+        ours = ShardSampler(n, world, rank, shuffle=True, seed=0)
+        assert list(ours) == ref and len(ours) == len(ref)
+    s = ShardSampler(n, world, 0)
+    a = list(s)
+    s.set_epoch(1)
+    assert list(s) != a or n < 3
+
+
+def test_batch_loader_and_synthetic_cifar():
+    from b200ddp.utils.data import BatchLoader, ShardSampler, SyntheticCIFAR10
+    ds = SyntheticCIFAR10(train=True, size=103)
+    assert ds.data.shape == (103, 32, 32, 3) and ds.data.dtype == np.uint8
+    loader = BatchLoader(ds, 32, sampler=ShardSampler(len(ds), 2, 1, shuffle=True, seed=0))
+    batches = list(loader)
+    assert len(batches) == len(loader) == 2 and batches[0][0].shape == (32, 32, 32, 3)
+    assert sum(b[0].shape[0] for b in batches) == len(loader.sampler) == 52        # uneven last batch (20)
+    assert batches[-1][0].shape[0] == 20
+
+
+def test_augment_reference_matches_torchvision_normalize():
+    import torchvision.transforms as T
+    from PIL import Image
+    from b200ddp.utils.data import CIFAR10_MEAN, CIFAR10_STD, augment_reference
+    img = torch.randint(0, 256, (3, 32, 32, 3), dtype=torch.uint8)
+    ident = torch.tensor([[4, 4, 0]] * 3)
+    out = augment_reference(img, offsets=ident)
+    tf = T.Compose([T.ToTensor(), T.Normalize(CIFAR10_MEAN, CIFAR10_STD)])
+    ref = torch.stack([tf(Image.fromarray(img[i].numpy())) for i in range(3)])
+    assert torch.allclose(out, ref, atol=1e-6)
+    flipped = augment_reference(img, offsets=torch.tensor([[4, 4, 1]] * 3))
+    assert torch.allclose(flipped, ref.flip(-1), atol=1e-6)
+
+
+# ------------------------------------------------------------------ bucket layout
+def test_bucket_assignment_matches_reference_reducer_sizes():
+    from b200ddp.models import get_model
+    from b200ddp.parallel.reducer import assign_buckets
+
+    def bucket_bytes(name):
+        params = list(reversed([p for p in get_model(name).parameters()]))
+        _, buckets, total = assign_buckets([p.numel() for p in params], 1 << 20, 25 << 20)
+        return [sum(params[i].numel() for i in b.param_ids) * 4 for b in buckets], [len(b.param_ids) for b in buckets]
+
+    assert bucket_bytes("custom") == ([248024], [10])
+    assert bucket_bytes("resnet18") == ([2052000, 28852224, 15853824], [2, 12, 48])
+    assert bucket_bytes("resnet50")[0] == [8196000, 31502336, 26255360, 26550272, 9724160]
+    ours = bucket_bytes("resnet18")[0]
+    model = get_model("resnet18")
+    idx = torch.distributed._compute_bucket_assignment_by_size(list(reversed(list(model.parameters()))), [1 << 20, 25 << 20])[0]
+    ps = list(reversed(list(model.parameters())))
+    assert ours == [sum(ps[i].numel() for i in b) * 4 for b in idx]
+
+
+# ------------------------------------------------------------------ models / checkpoints
+def test_state_dict_keys_match_torchvision_and_reference_net():
+    import torchvision
+    from b200ddp.models import get_model
+    for name, tv in (("resnet18", torchvision.models.resnet18), ("resnet50", torchvision.models.resnet50)):
+        a, b = get_model(name).state_dict(), tv().state_dict()
+        assert list(a.keys()) == list(b.keys())
+        assert all(a[k].shape == b[k].shape for k in a)
+    net = get_model("custom")
+    assert list(net.state_dict().keys()) == ["conv1.weight", "conv1.bias", "conv2.weight", "conv2.bias", "fc1.weight",
+                                             "fc1.bias", "fc2.weight", "fc2.bias", "fc3.weight", "fc3.bias"]
+    assert sum(p.numel() for p in net.parameters()) == 62006
+    assert sum(p.numel() for p in get_model("resnet18").parameters()) == 11689512
+
+
+def test_workshop_net_cpu_forward_equals_reference_definition():
+    if not os.path.isdir(REF_CODE):
+        pytest.skip("reference tree not mounted")
+    import importlib.util
+    sys.dont_write_bytecode = True
+    spec = importlib.util.spec_from_file_location("ref_inference", os.path.join(REF_CODE, "inference.py"))
+    ref = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ref)
+    from b200ddp.models import get_model
+    ours, theirs = get_model("custom"), ref.Net()
+    theirs.load_state_dict(ours.state_dict())
+    x = torch.randn(5, 3, 32, 32)
+    assert torch.allclose(ours(x), theirs(x), atol=1e-6)
+
+
+def test_checkpoint_roundtrip_and_reference_model_fn(tmp_path):
+    from b200ddp.models import get_model
+    from b200ddp.utils import checkpoint as ck
+    from b200ddp.workloads.inference import input_fn, model_fn, output_fn, predict_fn
+    net = get_model("custom")
+    path = ck.save_model(net, str(tmp_path))
+    sd = torch.load(path, map_location="cpu", weights_only=True)
+    assert not any(k.startswith("module.") for k in sd) and all(v.is_contiguous() for v in sd.values())
+    served = model_fn(str(tmp_path))
+    x = torch.randn(4, 3, 32, 32)
+    assert torch.allclose(served(x), net.eval()(x), atol=1e-6)
+    buf = __import__("io").BytesIO()
+    np.save(buf, x.numpy())
+    pred = predict_fn(input_fn(buf.getvalue(), "application/x-npy"), served)
+    assert len(json.loads(output_fn(pred))) == 4
+    if os.path.isdir(REF_CODE):            # the reference's unmodified serving hook loads our file
+        import importlib.util
+        sys.dont_write_bytecode = True
+        spec = importlib.util.spec_from_file_location("ref_inference2", os.path.join(REF_CODE, "inference.py"))
+        ref = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(ref)
+        assert torch.allclose(ref.model_fn(str(tmp_path))(x), net(x), atol=1e-6)
+    # full checkpoint (beyond the reference): resume restores weights, optimizer state and epoch
+    opt = torch.optim.SGD(net.parameters(), lr=0.1, momentum=0.9)
+    net(x).sum().backward()
+    opt.step()
+    full = ck.save_full(net, opt, 3, str(tmp_path / "checkpoint.pt"))
+    net2 = get_model("custom")
+    opt2 = torch.optim.SGD(net2.parameters(), lr=0.1, momentum=0.9)
+    assert ck.load_full(net2, opt2, full) == 3
+    assert all(torch.equal(a, b) for a, b in zip(net.state_dict().values(), net2.state_dict().values()))
+    assert len(opt2.state_dict()["state"]) == len(opt.state_dict()["state"])
+
+
+def test_native_library_builds_and_loads_without_gpu(native_lib):
+    assert native_lib.b200_version() >= 100
+    hdr = open(os.path.join(ROOT, "include", "b200ddp.h")).read()
+    import ctypes
+    for sym in ("b200_allreduce", "b200_conv_fwd", "b200_conv_dgrad", "b200_conv_wgrad", "b200_bn_stats", "b200_sgd_momentum",
+                "b200_adam", "b200_softmax_xent", "b200_augment", "b200_trojan_stamp", "b200_broadcast", "b200_barrier"):
+        assert hasattr(native_lib, sym) and sym in hdr
+
+
+def test_sass_has_blackwell_tensor_core_and_multimem_instructions():
+    """The conv kernel must be tcgen05/TMEM code, the all-reduce must carry multimem (NVLS) instructions."""
+    obj = os.path.join(ROOT, "build", "conv_tc.o")
+    if not os.path.exists(obj):
+        from b200ddp.ops.build import build
+        build()
+    sass = subprocess.run(["cuobjdump", "-sass", obj], capture_output=True, text=True).stdout
+    assert "UTCHMMA" in sass and "LDTM" in sass and "LDGSTS" in sass
+    ptx_or_sass = subprocess.run(["cuobjdump", "-sass", os.path.join(ROOT, "build", "comm.o")], capture_output=True, text=True).stdout
+    assert "LDGMC" in ptx_or_sass            # SASS of multimem.ld_reduce (multimem.st shows as a multicast STG)
