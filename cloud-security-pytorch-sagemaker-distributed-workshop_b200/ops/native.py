@@ -38,23 +38,23 @@ def scratch(device: torch.device) -> torch.Tensor:
     return t
 
 
-_CONV_SCRATCH = {}
-CONV_SCRATCH_BYTES = 64 << 20
+class _SplitK:
+    """``SPLIT_K[0] = False`` pins conv/linear fwd+dgrad to one CTA per tile (``B200DDP_CONV_SPLITK=0``)."""
+
+    def __init__(self):
+        self._v = True
+        if __import__("os").environ.get("B200DDP_CONV_SPLITK", "1") in ("0", "false", "off"):
+            self[0] = False
+
+    def __getitem__(self, i):
+        return self._v
+
+    def __setitem__(self, i, v):
+        self._v = bool(v)
+        L.lib().b200_conv_set_split_k(c_int(int(self._v)))
 
 
-SPLIT_K = [__import__("os").environ.get("B200DDP_CONV_SPLITK", "1") not in ("0", "false", "off")]
-
-
-def conv_scratch(device: torch.device) -> Optional[torch.Tensor]:
-    """Split-K scratch of the tensor-core conv/linear kernels (tile tickets + fp32 partial tiles)."""
-    if not SPLIT_K[0]:
-        return None
-    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
-    t = _CONV_SCRATCH.get(key)
-    if t is None:
-        t = torch.zeros(CONV_SCRATCH_BYTES, dtype=torch.uint8, device=device)
-        _CONV_SCRATCH[key] = t
-    return t
+SPLIT_K = _SplitK()
 
 
 def _cl_ok(x: torch.Tensor) -> bool:
@@ -89,9 +89,8 @@ def conv_fwd(x: torch.Tensor, w_krsc: torch.Tensor, bias: Optional[torch.Tensor]
     Ho, Wo = conv_out_hw(H, W, R, S, stride, pad)
     y = empty_act(N, K, Ho, Wo, x.device)
     g = _geom(N, H, W, C, K, R, S, stride, pad)
-    sc = conv_scratch(x.device)
     L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w_krsc), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
-                                  L.ptr(sc), c_size_t(sc.numel() if sc is not None else 0), L.stream_ptr()), "conv_fwd")
+                                  L.stream_ptr()), "conv_fwd")
     return y
 
 
@@ -101,9 +100,7 @@ def conv_dgrad(dy: torch.Tensor, w_krsc: torch.Tensor, x_shape, stride: int, pad
     assert _cl_ok(dy)
     dx = empty_act(N, C, H, W, dy.device)
     g = _geom(N, H, W, C, K, R, S, stride, pad)
-    sc = conv_scratch(dy.device)
-    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.ptr(sc), c_size_t(sc.numel() if sc is not None else 0),
-                                    L.stream_ptr()), "conv_dgrad")
+    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.stream_ptr()), "conv_dgrad")
     return dx
 
 
@@ -126,9 +123,8 @@ def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], r
     assert x.is_contiguous() and w.is_contiguous()
     y = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
     g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
-    sc = conv_scratch(x.device)
     L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
-                                  L.ptr(sc), c_size_t(sc.numel() if sc is not None else 0), L.stream_ptr()), "linear_fwd")
+                                  L.stream_ptr()), "linear_fwd")
     return y
 
 
@@ -137,9 +133,7 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     K = w.shape[1]
     dx = torch.empty((M, K), dtype=torch.bfloat16, device=dy.device)
     g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
-    sc = conv_scratch(dy.device)
-    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w), L.ptr(dx), byref(g), L.ptr(sc), c_size_t(sc.numel() if sc is not None else 0),
-                                    L.stream_ptr()), "linear_dgrad")
+    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w), L.ptr(dx), byref(g), L.stream_ptr()), "linear_dgrad")
     return dx
 
 

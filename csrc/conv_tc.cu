@@ -25,9 +25,13 @@
 // Small-problem machinery (the reference's resnet18 runs at 8x8 .. 1x1 spatial):
 //   * filter taps that can never touch a real pixel (e.g. 8 of the 9 taps of a 3x3 conv on a 1x1 map)
 //     are dropped from the K loop (FWD/DGRAD) or from the grid (WGRAD) — decided on the host;
-//   * FWD/DGRAD split K across CTAs when the tile grid cannot fill 148 SMs: every split writes its fp32
-//     partial into the tile's accumulator in scratch (red.add.v4.f32); the last CTA of a tile (ticket
-//     counter) reads the sum, re-zeroes the accumulator and ticket (self-resetting) and runs the epilogue.
+//   * split-K inside a thread-block cluster when the tile grid cannot fill 148 SMs: the 2/4/8 CTAs of a
+//     cluster (hardware co-scheduled) each accumulate a K slice in their own TMEM, stage the fp32 partial
+//     in shared memory, and after a cluster barrier every CTA reduces its BN/ZC column slice over all peers
+//     through distributed shared memory (ld.shared::cluster) and runs the epilogue for it: no atomics, no
+//     global scratch, deterministic.  WGRAD additionally spreads clusters over K and joins them with red.add.
+#include <stdlib.h>
+
 #include <algorithm>
 
 #include "tc_ptx.cuh"
@@ -43,7 +47,7 @@ constexpr int STAGES = 6;
 constexpr int LAG = 4;                 // cp.async groups kept in flight behind the newest one
 constexpr int PRODUCERS = 128;
 constexpr int THREADS = PRODUCERS + 32;
-constexpr size_t kSplitCounterBytes = 16384;   // 4096 tile tickets at the head of the split-K scratch
+bool g_split_k = true;                 // b200_conv_set_split_k(0) pins FWD/DGRAD to one CTA per tile (reproducibility checks)
 
 struct ConvParams {
   const __nv_bfloat16* x;    // image-side tensor (FWD/WGRAD: input, DGRAD: unused)
@@ -51,8 +55,6 @@ struct ConvParams {
   const __nv_bfloat16* dy;   // output-side tensor (DGRAD/WGRAD)
   void* out;                 // FWD: y bf16 [M][Cout]; DGRAD: dx bf16 [M][Cin]; WGRAD: dw fp32 [Cout][R*S*Cin]
   const float* bias;         // FWD only, may be null
-  float* partials;           // split-K scratch (FWD/DGRAD), fp32 accumulators [tile][128][BN], zero between uses
-  unsigned* tickets;         // split-K tile tickets
   int N, H, W, C;            // input geometry (C = Cin)
   int Kc, R, S, stride, pad; // Kc = Cout
   int Ho, Wo;
@@ -61,7 +63,6 @@ struct ConvParams {
   uint32_t nvk;              // number of (virtual) k-blocks that are executed
   uint32_t kb_per_split;     // virtual k-blocks per grid.z slice
   uint32_t cpt;              // k-blocks per filter tap (0: no tap skipping, virtual == real)
-  uint32_t splits;
   unsigned long long tapmask;  // bit t set: tap t can touch a real pixel somewhere in the tensor
   uint8_t tap_list[64];      // the set bits of tapmask, ascending
   FastDiv div_c, div_s, div_kc, div_wo, div_ho, div_w, div_h, div_cpt;
@@ -83,7 +84,43 @@ __device__ __forceinline__ uint32_t virt2kb(const ConvParams& p, uint32_t v) {
   return (uint32_t)p.tap_list[q] * p.cpt + (v - q * p.cpt);
 }
 
-template <int MODE, int BN>
+// Write NCOLS accumulator columns [nn0, nn0+NCOLS) of GEMM row m.  FWD: +bias, ReLU, bf16.  DGRAD: bf16.
+// WGRAD: fp32 red.add into the gradient arena.
+template <int MODE, int NCOLS>
+__device__ __forceinline__ void epilogue_store(const ConvParams& p, uint32_t m, uint32_t nn0, float* f) {
+  if (m >= p.gemm_m || nn0 >= p.gemm_n) return;
+  if (MODE == MODE_WGRAD) {
+    float* dst = reinterpret_cast<float*>(p.out) + (size_t)m * p.gemm_n + nn0;
+    if (nn0 + NCOLS <= p.gemm_n) {
+#pragma unroll
+      for (int q = 0; q < NCOLS / 4; ++q)
+        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + 4 * q), "f"(f[4 * q]), "f"(f[4 * q + 1]),
+                     "f"(f[4 * q + 2]), "f"(f[4 * q + 3])
+                     : "memory");
+    } else {
+      for (int q = 0; q < NCOLS; ++q)
+        if (nn0 + q < p.gemm_n) atomicAdd(dst + q, f[q]);
+    }
+  } else {
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.gemm_n + nn0;
+    if (MODE == MODE_FWD) {
+#pragma unroll
+      for (int q = 0; q < NCOLS; ++q) {
+        if (p.bias != nullptr && nn0 + q < p.gemm_n) f[q] += __ldg(p.bias + nn0 + q);
+        if (p.relu) f[q] = fmaxf(f[q], 0.f);
+      }
+    }
+    if (nn0 + NCOLS <= p.gemm_n) {
+#pragma unroll
+      for (int q = 0; q < NCOLS / 8; ++q) *reinterpret_cast<bf16x8*>(dst + 8 * q) = float_to_bf16x8(f + 8 * q);
+    } else {
+      for (int q = 0; q < NCOLS; ++q)
+        if (nn0 + q < p.gemm_n) dst[q] = __float2bfloat16(f[q]);
+    }
+  }
+}
+
+template <int MODE, int BN, int ZC>
 __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_constant__ ConvParams p) {
   using C = Cfg<MODE, BN>;
   const uint32_t m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
@@ -102,7 +139,6 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_consta
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
-  uint32_t* last_flag = tmem_slot + 1;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t v_begin = blockIdx.z * p.kb_per_split;
@@ -290,94 +326,38 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_consta
     // =============================== EPILOGUE (TMEM -> registers -> global) ===============================
     const uint32_t row = warp * 32 + lane;          // accumulator row == TMEM lane
     const uint32_t m = m0 + row;
-    bool do_final = true;
-    if (MODE != MODE_WGRAD && p.splits > 1) {
-      // ---- split-K: add this CTA's fp32 partial into the tile accumulator (scratch, zero between uses),
-      // elect the last CTA of the tile
-      const uint32_t tile_id = blockIdx.y * gridDim.x + blockIdx.x;
-      float* mine = p.partials + (size_t)tile_id * (BM * BN) + (size_t)row * BN;
-      if (nkb > 0) {
+    if (ZC == 1) {
+      if (nkb > 0 || MODE != MODE_WGRAD) {
 #pragma unroll 1
         for (int cb = 0; cb < BN / 32; ++cb) {
-          uint32_t v[32];
-          tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + cb * 32, v);
+          float f[32];
+          if (nkb > 0) {
+            uint32_t v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + cb * 32, v);
 #pragma unroll
-          for (int q = 0; q < 8; ++q)
-            asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mine + cb * 32 + 4 * q),
-                         "f"(__uint_as_float(v[4 * q])), "f"(__uint_as_float(v[4 * q + 1])),
-                         "f"(__uint_as_float(v[4 * q + 2])), "f"(__uint_as_float(v[4 * q + 3]))
-                         : "memory");
+            for (int q = 0; q < 32; ++q) f[q] = __uint_as_float(v[q]);
+          } else {
+#pragma unroll
+            for (int q = 0; q < 32; ++q) f[q] = 0.f;
+          }
+          epilogue_store<MODE, 32>(p, m, n0 + cb * 32, f);
         }
       }
-      __threadfence();
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (tid == 0) {
-        const unsigned ticket = atomicAdd(p.tickets + tile_id, 1u);
-        const unsigned last = (ticket == p.splits - 1) ? 1u : 0u;
-        if (last) p.tickets[tile_id] = 0u;     // self-resetting
-        *last_flag = last;
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      do_final = (*last_flag != 0u);
-      if (do_final) __threadfence();
-    }
-    if (do_final && (nkb > 0 || MODE != MODE_WGRAD)) {
+    } else {
+      // ---- cluster split-K: the ZC CTAs of a cluster hold partial sums of the same tile.  Stage the
+      // partial in shared memory (column-major: conflict-free, one row per thread) ...
+      float* stage = reinterpret_cast<float*>(smem);        // the operand ring is idle now: all MMAs retired
 #pragma unroll 1
       for (int cb = 0; cb < BN / 32; ++cb) {
         uint32_t v[32];
-        if (MODE != MODE_WGRAD && p.splits > 1) {
-          const uint32_t tile_id = blockIdx.y * gridDim.x + blockIdx.x;
-          float4* src = reinterpret_cast<float4*>(p.partials + (size_t)tile_id * (BM * BN) + (size_t)row * BN + cb * 32);
-#pragma unroll
-          for (int q = 0; q < 8; ++q) {
-            const float4 t = __ldcg(src + q);
-            v[4 * q] = __float_as_uint(t.x); v[4 * q + 1] = __float_as_uint(t.y);
-            v[4 * q + 2] = __float_as_uint(t.z); v[4 * q + 3] = __float_as_uint(t.w);
-          }
-#pragma unroll
-          for (int q = 0; q < 8; ++q) __stcg(src + q, make_float4(0.f, 0.f, 0.f, 0.f));   // ready for the next launch
-        } else if (nkb > 0) {
+        if (nkb > 0) {
           tmem_ld32(tmem_base + ((uint32_t)(warp * 32) << 16) + cb * 32, v);
         } else {
 #pragma unroll
           for (int q = 0; q < 32; ++q) v[q] = 0u;
         }
-        const uint32_t nn0 = n0 + cb * 32;
-        if (m < p.gemm_m) {
-          if (MODE == MODE_WGRAD) {
-            float* dst = reinterpret_cast<float*>(p.out) + (size_t)m * p.gemm_n + nn0;
-            if (nn0 + 32 <= p.gemm_n) {
 #pragma unroll
-              for (int q = 0; q < 8; ++q)
-                asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + 4 * q), "f"(__uint_as_float(v[4 * q])),
-                             "f"(__uint_as_float(v[4 * q + 1])), "f"(__uint_as_float(v[4 * q + 2])),
-                             "f"(__uint_as_float(v[4 * q + 3]))
-                             : "memory");
-            } else {
-              for (int q = 0; q < 32; ++q)
-                if (nn0 + q < p.gemm_n) atomicAdd(dst + q, __uint_as_float(v[q]));
-            }
-          } else {
-            __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.gemm_n + nn0;
-            float f[32];
-#pragma unroll
-            for (int q = 0; q < 32; ++q) {
-              float a = __uint_as_float(v[q]);
-              if (MODE == MODE_FWD) {
-                if (p.bias != nullptr && nn0 + q < p.gemm_n) a += __ldg(p.bias + nn0 + q);
-                if (p.relu) a = fmaxf(a, 0.f);
-              }
-              f[q] = a;
-            }
-            if (nn0 + 32 <= p.gemm_n) {
-#pragma unroll
-              for (int q = 0; q < 4; ++q) *reinterpret_cast<bf16x8*>(dst + 8 * q) = float_to_bf16x8(f + 8 * q);
-            } else {
-              for (int q = 0; q < 32; ++q)
-                if (nn0 + q < p.gemm_n) dst[q] = __float2bfloat16(f[q]);
-            }
-          }
-        }
+        for (int q = 0; q < 32; ++q) stage[(cb * 32 + q) * BM + row] = __uint_as_float(v[q]);
       }
     }
   } else if (lane == 0 && nkb > 0) {
@@ -400,6 +380,29 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_consta
       if (it + 1 == nkb) umma_commit(tmem_full);  // accumulator complete
     }
   }
+  if (ZC > 1) {
+    // ... then every CTA reduces its BN/ZC column slice over all peers through distributed shared memory
+    // (ld.shared::cluster) and runs the epilogue for that slice.  No atomics, no global scratch.
+    cluster_sync_all();
+    if (warp < 4) {
+      constexpr int SLICE = BN / ZC;
+      const uint32_t rank = cluster_ctarank();
+      const uint32_t row = warp * 32 + lane;
+      const uint32_t m = m0 + row;
+      const uint32_t stage_u32 = smem_u32(smem);
+      float f[SLICE];
+#pragma unroll
+      for (int q = 0; q < SLICE; ++q) f[q] = 0.f;
+#pragma unroll 1
+      for (uint32_t z = 0; z < (uint32_t)ZC; ++z) {
+        const uint32_t base = dsmem_addr(stage_u32 + ((rank * SLICE) * BM + row) * 4u, z);
+#pragma unroll
+        for (int q = 0; q < SLICE; ++q) f[q] += ld_dsmem_f32(base + (uint32_t)q * BM * 4u);
+      }
+      if (MODE != MODE_WGRAD || p.nvk > 0) epilogue_store<MODE, SLICE>(p, m, n0 + rank * SLICE, f);
+    }
+    cluster_sync_all();      // nobody leaves while a peer may still read its shared memory
+  }
   tc_fence_before();
   __syncthreads();
   if (warp == 4) {
@@ -409,17 +412,40 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_consta
 }
 
 // ------------------------------------------------------------------------------------------------
-template <int MODE, int BN>
-int launch(const ConvParams& p, dim3 grid, cudaStream_t s) {
+template <int MODE, int BN, int ZC>
+int launch_zc(const ConvParams& p, dim3 grid, cudaStream_t s) {
   using C = Cfg<MODE, BN>;
   static bool attr_set = false;
   if (!attr_set) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<MODE, BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<MODE, BN, ZC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_set = true;
   }
-  conv_tc_kernel<MODE, BN><<<grid, THREADS, C::SMEM_BYTES, s>>>(p);
-  B200_CHECK_LAUNCH();
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(THREADS, 1, 1);
+  cfg.dynamicSmemBytes = C::SMEM_BYTES;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = ZC;
+  cfg.attrs = attr;
+  cfg.numAttrs = ZC > 1 ? 1 : 0;
+  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<MODE, BN, ZC>, p));
   return 0;
+}
+
+template <int MODE, int BN>
+int launch(const ConvParams& p, dim3 grid, uint32_t zc, cudaStream_t s) {
+  switch (zc) {
+    case 1: return launch_zc<MODE, BN, 1>(p, grid, s);
+    case 2: return launch_zc<MODE, BN, 2>(p, grid, s);
+    case 4: return launch_zc<MODE, BN, 4>(p, grid, s);
+    case 8: return launch_zc<MODE, BN, 8>(p, grid, s);
+    default: b200_set_error("cluster split %u is not 1, 2, 4 or 8", zc); return B200_ERR_ARG;
+  }
 }
 
 int fill_common(ConvParams& p, const b200_conv_geom* g) {
@@ -437,7 +463,6 @@ int fill_common(ConvParams& p, const b200_conv_geom* g) {
   p.div_wo = make_fastdiv(p.Wo); p.div_ho = make_fastdiv(p.Ho);
   p.div_w = make_fastdiv(p.W); p.div_h = make_fastdiv(p.H);
   p.div_cpt = make_fastdiv(1);
-  p.splits = 1;
   // ---- filter taps that can touch a real pixel.  The relation "input row h pairs with output row ho
   // through tap r" (h = ho*stride - pad + r) is the same for fwd, dgrad and wgrad.
   unsigned long long mask = 0;
@@ -477,28 +502,46 @@ void plan_k(ConvParams& p, uint32_t cdim) {
   p.kb_per_split = p.nvk;
 }
 
-// split K so the grid covers the machine when the tile grid alone cannot (small M x N)
-void plan_splits(ConvParams& p, uint32_t tiles, uint32_t bn, void* scratch, size_t scratch_bytes) {
-  p.splits = 1;
+
+// K split inside a thread-block cluster (DSMEM reduction): largest power of two <= min(8, want)
+// Clusters of 4 pack the 16..20-SM GPCs of a B200 almost fully (36 x 4 = 144 of 148 SMs); clusters of 8
+// leave SMs stranded and measured ~2x slower on the resnet18 layer shapes.  B200DDP_CLUSTER_MAX overrides.
+uint32_t cluster_cap() {
+  static uint32_t cap = 0;
+  if (cap == 0) {
+    const char* e = getenv("B200DDP_CLUSTER_MAX");
+    const int v = e ? atoi(e) : 4;
+    cap = (v >= 8) ? 8u : (v >= 4) ? 4u : (v >= 2) ? 2u : 1u;
+  }
+  return cap;
+}
+uint32_t cluster_split(uint32_t want) {
+  uint32_t zc = 1;
+  while (zc * 2 <= want && zc * 2 <= cluster_cap()) zc *= 2;
+  return zc;
+}
+
+// FWD/DGRAD: split K over a cluster when the tile grid alone cannot fill the machine
+uint32_t plan_cluster(ConvParams& p, uint32_t tiles) {
   const uint32_t sms = (uint32_t)b200_num_sms();
-  if (scratch == nullptr || tiles * 2 > sms || tiles > 4096 || p.nvk < 4) return;
-  uint32_t want = sms / tiles;                           // one wave: tiles * splits <= #SMs (1 CTA per SM)
-  const uint32_t by_k = p.nvk / 2;                       // >= 2 k-blocks per split
-  if (want > by_k) want = by_k;
-  if (want > 16) want = 16;
-  if (scratch_bytes < kSplitCounterBytes + (size_t)tiles * BM * bn * sizeof(float)) return;
-  if (want < 2) return;
-  p.kb_per_split = (p.nvk + want - 1) / want;
-  p.splits = (p.nvk + p.kb_per_split - 1) / p.kb_per_split;
-  if (p.splits < 2) { p.splits = 1; p.kb_per_split = p.nvk; return; }
-  p.tickets = reinterpret_cast<unsigned*>(scratch);
-  p.partials = reinterpret_cast<float*>(reinterpret_cast<char*>(scratch) + kSplitCounterBytes);
+  p.kb_per_split = p.nvk;
+  if (!g_split_k || tiles * 2 > sms || p.nvk < 4) return 1;
+  uint32_t want = sms / tiles;
+  if (want > p.nvk / 2) want = p.nvk / 2;            // >= 2 k-blocks per CTA
+  const uint32_t zc = cluster_split(want);
+  p.kb_per_split = (p.nvk + zc - 1) / zc;
+  return zc;
 }
 
 }  // namespace
 
+extern "C" int b200_conv_set_split_k(int enabled) {
+  g_split_k = enabled != 0;
+  return 0;
+}
+
 extern "C" int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g,
-                             int relu, void* scratch, size_t scratch_bytes, void* stream) {
+                             int relu, void* stream) {
   ConvParams p;
   int rc = fill_common(p, g);
   if (rc) return rc;
@@ -509,13 +552,12 @@ extern "C" int b200_conv_fwd(const void* x, const void* w, const float* bias, vo
   const bool narrow = p.gemm_n <= 64;
   const uint32_t bn = narrow ? 64 : 128;
   dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, 1);
-  plan_splits(p, grid.x * grid.y, bn, scratch, scratch_bytes);
-  grid.z = p.splits;
-  return narrow ? launch<MODE_FWD, 64>(p, grid, (cudaStream_t)stream) : launch<MODE_FWD, 128>(p, grid, (cudaStream_t)stream);
+  const uint32_t zc = plan_cluster(p, grid.x * grid.y);
+  grid.z = zc;
+  return narrow ? launch<MODE_FWD, 64>(p, grid, zc, (cudaStream_t)stream) : launch<MODE_FWD, 128>(p, grid, zc, (cudaStream_t)stream);
 }
 
-extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* scratch,
-                               size_t scratch_bytes, void* stream) {
+extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream) {
   ConvParams p;
   int rc = fill_common(p, g);
   if (rc) return rc;
@@ -526,9 +568,9 @@ extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b2
   const bool narrow = p.gemm_n <= 64;
   const uint32_t bn = narrow ? 64 : 128;
   dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, 1);
-  plan_splits(p, grid.x * grid.y, bn, scratch, scratch_bytes);
-  grid.z = p.splits;
-  return narrow ? launch<MODE_DGRAD, 64>(p, grid, (cudaStream_t)stream) : launch<MODE_DGRAD, 128>(p, grid, (cudaStream_t)stream);
+  const uint32_t zc = plan_cluster(p, grid.x * grid.y);
+  grid.z = zc;
+  return narrow ? launch<MODE_DGRAD, 64>(p, grid, zc, (cudaStream_t)stream) : launch<MODE_DGRAD, 128>(p, grid, zc, (cudaStream_t)stream);
 }
 
 extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
@@ -559,17 +601,18 @@ extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b
     if (live_n_tiles == 0) return 0;
   }
   const uint32_t tiles = ((p.gemm_m + BM - 1) / BM) * live_n_tiles;
-  // split the position reduction so the grid covers the machine ~2x; >= 2 k-blocks per CTA
+  // split the position reduction so the grid covers the machine ~2x (>= 2 k-blocks per CTA): the `zc` CTAs of a
+  // cluster reduce through DSMEM so only one red.add per element leaves the cluster; `zo` such clusters
+  // accumulate through the atomics.
   uint32_t splits = (2u * (uint32_t)b200_num_sms() + tiles - 1) / tiles;
   if (max_splits > 0 && splits > (uint32_t)max_splits) splits = (uint32_t)max_splits;
   const uint32_t max_by_k = (kblocks + 1) / 2;
   if (splits > max_by_k) splits = max_by_k;
   if (splits < 1) splits = 1;
-  p.kb_per_split = (kblocks + splits - 1) / splits;
-  splits = (kblocks + p.kb_per_split - 1) / p.kb_per_split;
-  p.splits = 1;   // WGRAD reduces its splits with red.add, not through scratch
-  // virt2kb must be the identity for WGRAD even though cpt != 0
+  const uint32_t zc = cluster_split(splits);
+  const uint32_t zo = (splits + zc - 1) / zc;
+  p.kb_per_split = (kblocks + zo * zc - 1) / (zo * zc);
   p.div_cpt = make_fastdiv(1);
-  dim3 grid((p.gemm_m + BM - 1) / BM, n_tiles, splits);
-  return narrow ? launch<MODE_WGRAD, 64>(p, grid, (cudaStream_t)stream) : launch<MODE_WGRAD, 128>(p, grid, (cudaStream_t)stream);
+  dim3 grid((p.gemm_m + BM - 1) / BM, n_tiles, zo * zc);
+  return narrow ? launch<MODE_WGRAD, 64>(p, grid, zc, (cudaStream_t)stream) : launch<MODE_WGRAD, 128>(p, grid, zc, (cudaStream_t)stream);
 }

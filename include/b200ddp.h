@@ -170,12 +170,12 @@ typedef struct b200_conv_geom {
   int K;          /* output channels */
   int R, S, stride, pad;
 } b200_conv_geom;
-/* `scratch` (may be NULL: no split-K) is global memory beyond inputs/outputs: 16 KiB of tile tickets
- * followed by fp32 partial tiles.  Zero before first use; every launch leaves the tickets at zero. */
+/* Small problems split K over a thread-block cluster (DSMEM reduction; no scratch).  b200_conv_set_split_k(0)
+ * pins fwd/dgrad to one CTA per tile. */
+int b200_conv_set_split_k(int enabled);
 int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g, int relu,
-                  void* scratch, size_t scratch_bytes, void* stream);
-int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* scratch,
-                    size_t scratch_bytes, void* stream);
+                  void* stream);
+int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream);
 int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
                     void* stream);
 
