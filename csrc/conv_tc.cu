@@ -30,6 +30,7 @@
 //     in shared memory, and after a cluster barrier every CTA reduces its BN/ZC column slice over all peers
 //     through distributed shared memory (ld.shared::cluster) and runs the epilogue for it: no atomics, no
 //     global scratch, deterministic.  WGRAD additionally spreads clusters over K and joins them with red.add.
+#include <cuda.h>
 #include <stdlib.h>
 
 #include <algorithm>
@@ -63,6 +64,7 @@ struct ConvParams {
   uint32_t nvk;              // number of (virtual) k-blocks that are executed
   uint32_t kb_per_split;     // virtual k-blocks per grid.z slice
   uint32_t cpt;              // k-blocks per filter tap (0: no tap skipping, virtual == real)
+  uint32_t a_tma, b_tma;     // operand staged by TMA (plain 2-D matrix) instead of the cp.async gather
   unsigned long long tapmask;  // bit t set: tap t can touch a real pixel somewhere in the tensor
   uint8_t tap_list[64];      // the set bits of tapmask, ascending
   FastDiv div_c, div_s, div_kc, div_wo, div_ho, div_w, div_h, div_cpt;
@@ -121,7 +123,9 @@ __device__ __forceinline__ void epilogue_store(const ConvParams& p, uint32_t m, 
 }
 
 template <int MODE, int BN, int ZC>
-__global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_constant__ ConvParams p) {
+__global__ void __launch_bounds__(THREADS, 1)
+conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUtensorMap tmA,
+               const __grid_constant__ CUtensorMap tmB) {
   using C = Cfg<MODE, BN>;
   const uint32_t m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   if (MODE == MODE_WGRAD && p.cpt != 0) {
@@ -147,11 +151,14 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_consta
 
   if (tid == 0) {
     for (int s = 0; s < STAGES; ++s) {
-      mbar_init(&full_bar[s], PRODUCERS);
+      // arrivals per stage: the 128 gather threads (if any operand still uses cp.async) + the TMA-issuing thread
+      mbar_init(&full_bar[s], ((p.a_tma & p.b_tma) ? 0u : (uint32_t)PRODUCERS) + ((p.a_tma | p.b_tma) ? 1u : 0u));
       mbar_init(&empty_bar[s], 1);
     }
     mbar_init(tmem_full, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    if (p.a_tma) tma_prefetch_desc(&tmA);
+    if (p.b_tma) tma_prefetch_desc(&tmB);
   }
   if (warp == 4) tmem_alloc(tmem_slot, BN);
   tc_fence_before();
@@ -209,7 +216,9 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_consta
         const uint32_t sa = smem_base + stage * C::STAGE_BYTES, sb = sa + C::A_BYTES;
 
         // ------------------------------- A operand -------------------------------
-        if (MODE == MODE_FWD || MODE == MODE_DGRAD) {
+        if (p.a_tma) {
+          // plain 2-D operand: fetched by TMA below
+        } else if (MODE == MODE_FWD || MODE == MODE_DGRAD) {
           const uint32_t j = tid & 7;
           const uint32_t k = kb * BK + j * 8;
           const bool k_ok = k < p.gemm_k;
@@ -257,7 +266,9 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_consta
         }
 
         // ------------------------------- B operand -------------------------------
-        if (MODE == MODE_FWD) {          // weight rows, K-major: BN rows x 8 chunks
+        if (p.b_tma) {
+          // plain 2-D operand: fetched by TMA below
+        } else if (MODE == MODE_FWD) {          // weight rows, K-major: BN rows x 8 chunks
           const uint32_t j = tid & 7;
           const uint32_t k = kb * BK + j * 8;
           const bool k_ok = k < p.gemm_k;
@@ -305,17 +316,34 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_consta
             cp_async16(sb + (c >> 3) * (BK * 128) + swz(row, c & 7), src, ok);
           }
         }
-        cp_async_commit();
-        if (it >= LAG) {
-          cp_async_wait<LAG>();          // group (it - LAG) has landed
-          fence_proxy_async();           // generic-proxy writes -> visible to the async proxy (tcgen05)
-          mbar_arrive(&full_bar[(it - LAG) % STAGES]);
+        if ((p.a_tma | p.b_tma) && tid == 0) {
+          // ---- TMA: one thread arms the stage barrier with the byte count and issues the tile loads; the
+          // hardware swizzles (128B) on the way in and zero-fills rows/columns beyond the tensor
+          const uint32_t bytes = (p.a_tma ? (uint32_t)C::A_BYTES : 0u) + (p.b_tma ? (uint32_t)C::B_BYTES : 0u);
+          mbar_arrive_expect_tx(&full_bar[stage], bytes);
+          if (p.a_tma) {
+            if (MODE == MODE_WGRAD) {         // A^T tile: 64 positions x 128 co as two 64-wide groups
+              tma_load_2d(sa, &tmA, (int)m0, (int)(kb * BK), &full_bar[stage]);
+              tma_load_2d(sa + BK * 128, &tmA, (int)m0 + 64, (int)(kb * BK), &full_bar[stage]);
+            } else {                          // [M][K] matrix (1x1 conv, stride 1 / linear)
+              tma_load_2d(sa, &tmA, (int)(kb * BK), (int)m0, &full_bar[stage]);
+            }
+          }
+          if (p.b_tma) tma_load_2d(sb, &tmB, (int)(kb * BK), (int)n0, &full_bar[stage]);   // weight rows [Cout][K]
+        }
+        if (!(p.a_tma & p.b_tma)) {
+          cp_async_commit();
+          if (it >= LAG) {
+            cp_async_wait<LAG>();          // group (it - LAG) has landed
+            fence_proxy_async();           // generic-proxy writes -> visible to the async proxy (tcgen05)
+            mbar_arrive(&full_bar[(it - LAG) % STAGES]);
+          }
         }
       }
-      // drain the last min(LAG, nkb) groups
-      cp_async_wait<0>();
-      fence_proxy_async();
-      {
+      if (!(p.a_tma & p.b_tma)) {
+        // drain the last min(LAG, nkb) groups
+        cp_async_wait<0>();
+        fence_proxy_async();
         const uint32_t first = nkb > LAG ? nkb - LAG : 0;
         for (uint32_t it = first; it < nkb; ++it) mbar_arrive(&full_bar[it % STAGES]);
       }
@@ -413,7 +441,7 @@ __global__ void __launch_bounds__(THREADS, 1) conv_tc_kernel(const __grid_consta
 
 // ------------------------------------------------------------------------------------------------
 template <int MODE, int BN, int ZC>
-int launch_zc(const ConvParams& p, dim3 grid, cudaStream_t s) {
+int launch_zc(const ConvParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, dim3 grid, cudaStream_t s) {
   using C = Cfg<MODE, BN>;
   static bool attr_set = false;
   if (!attr_set) {
@@ -433,19 +461,54 @@ int launch_zc(const ConvParams& p, dim3 grid, cudaStream_t s) {
   attr[0].val.clusterDim.z = ZC;
   cfg.attrs = attr;
   cfg.numAttrs = ZC > 1 ? 1 : 0;
-  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<MODE, BN, ZC>, p));
+  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<MODE, BN, ZC>, p, tmA, tmB));
   return 0;
 }
 
 template <int MODE, int BN>
-int launch(const ConvParams& p, dim3 grid, uint32_t zc, cudaStream_t s) {
+int launch(const ConvParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, dim3 grid, uint32_t zc, cudaStream_t s) {
   switch (zc) {
-    case 1: return launch_zc<MODE, BN, 1>(p, grid, s);
-    case 2: return launch_zc<MODE, BN, 2>(p, grid, s);
-    case 4: return launch_zc<MODE, BN, 4>(p, grid, s);
-    case 8: return launch_zc<MODE, BN, 8>(p, grid, s);
+    case 1: return launch_zc<MODE, BN, 1>(p, tmA, tmB, grid, s);
+    case 2: return launch_zc<MODE, BN, 2>(p, tmA, tmB, grid, s);
+    case 4: return launch_zc<MODE, BN, 4>(p, tmA, tmB, grid, s);
+    case 8: return launch_zc<MODE, BN, 8>(p, tmA, tmB, grid, s);
     default: b200_set_error("cluster split %u is not 1, 2, 4 or 8", zc); return B200_ERR_ARG;
   }
+}
+
+// ---- TMA descriptors (cuTensorMapEncodeTiled through the runtime's driver entry point) -------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+bool g_use_tma = true;
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult st;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &st) == cudaSuccess &&
+        st == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(f);
+    else
+      cudaGetLastError();
+    const char* e = getenv("B200DDP_TMA");
+    if (e && (e[0] == '0')) g_use_tma = false;
+  }
+  return g_use_tma ? fn : nullptr;
+}
+// bf16 row-major matrix [outer][inner] -> boxes of box_outer rows x 64 elements (128 B), 128B swizzle
+bool make_tmap_2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint32_t box_outer) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (fn == nullptr || (reinterpret_cast<uintptr_t>(base) & 15) != 0 || (inner * 2) % 16 != 0) return false;
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {inner * 2};
+  cuuint32_t box[2] = {64, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  return fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 int fill_common(ConvParams& p, const b200_conv_geom* g) {
@@ -554,7 +617,14 @@ extern "C" int b200_conv_fwd(const void* x, const void* w, const float* bias, vo
   dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, 1);
   const uint32_t zc = plan_cluster(p, grid.x * grid.y);
   grid.z = zc;
-  return narrow ? launch<MODE_FWD, 64>(p, grid, zc, (cudaStream_t)stream) : launch<MODE_FWD, 128>(p, grid, zc, (cudaStream_t)stream);
+  CUtensorMap tmA, tmB;
+  memset(&tmA, 0, sizeof(tmA));
+  memset(&tmB, 0, sizeof(tmB));
+  p.b_tma = make_tmap_2d(&tmB, w, p.gemm_k, p.gemm_n, bn) ? 1u : 0u;                       // weights [Cout][R*S*C]
+  const bool plain = p.R == 1 && p.S == 1 && p.stride == 1 && p.pad == 0;
+  p.a_tma = (plain && make_tmap_2d(&tmA, x, p.gemm_k, p.gemm_m, BM)) ? 1u : 0u;             // x as [M][C]
+  return narrow ? launch<MODE_FWD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
+                : launch<MODE_FWD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
 }
 
 extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream) {
@@ -570,7 +640,13 @@ extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b2
   dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, 1);
   const uint32_t zc = plan_cluster(p, grid.x * grid.y);
   grid.z = zc;
-  return narrow ? launch<MODE_DGRAD, 64>(p, grid, zc, (cudaStream_t)stream) : launch<MODE_DGRAD, 128>(p, grid, zc, (cudaStream_t)stream);
+  CUtensorMap tmA, tmB;
+  memset(&tmA, 0, sizeof(tmA));
+  memset(&tmB, 0, sizeof(tmB));
+  const bool plain = p.R == 1 && p.S == 1 && p.stride == 1 && p.pad == 0;
+  p.a_tma = (plain && make_tmap_2d(&tmA, dy, p.gemm_k, p.gemm_m, BM)) ? 1u : 0u;            // dy as [M][Cout]
+  return narrow ? launch<MODE_DGRAD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
+                : launch<MODE_DGRAD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
 }
 
 extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
@@ -614,5 +690,10 @@ extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b
   p.kb_per_split = (kblocks + zo * zc - 1) / (zo * zc);
   p.div_cpt = make_fastdiv(1);
   dim3 grid((p.gemm_m + BM - 1) / BM, n_tiles, zo * zc);
-  return narrow ? launch<MODE_WGRAD, 64>(p, grid, zc, (cudaStream_t)stream) : launch<MODE_WGRAD, 128>(p, grid, zc, (cudaStream_t)stream);
+  CUtensorMap tmA, tmB;
+  memset(&tmA, 0, sizeof(tmA));
+  memset(&tmB, 0, sizeof(tmB));
+  p.a_tma = make_tmap_2d(&tmA, dy, p.gemm_m, p.gemm_k, BK) ? 1u : 0u;      // dy as [positions][Cout], 64 x 64 boxes
+  return narrow ? launch<MODE_WGRAD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
+                : launch<MODE_WGRAD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
 }
