@@ -31,7 +31,7 @@ import torch
 import torch.nn as nn
 
 from . import process_group as pg
-from .reducer import ALIGN_ELEMS, Reducer, assign_buckets
+from .reducer import ALIGN_ELEMS, NativeReducer, Reducer, assign_buckets
 from ..utils.config import CommConfig
 from ..utils.logging import get_logger
 
@@ -127,8 +127,12 @@ class DistributedDataParallel(nn.Module):
         # ---- buffers: one byte arena so the per-forward sync is one broadcast
         self._setup_buffers()
 
-        self.reducer = Reducer(self.flat_grads, buckets, param_bucket, self.world_size,
-                               self.backend, comm=self.comm, arena_offset_bytes=grad_off_bytes)
+        if self.backend == "b200" and self.comm is not None:
+            self.reducer = NativeReducer(self.flat_grads, buckets, param_bucket, self.world_size, self.comm,
+                                         arena_offset_bytes=grad_off_bytes)
+        else:
+            self.reducer = Reducer(self.flat_grads, buckets, param_bucket, self.world_size,
+                                   self.backend, comm=self.comm, arena_offset_bytes=grad_off_bytes)
         for i, p in enumerate(self.params):
             p.register_post_accumulate_grad_hook(self._make_hook(i))
 

@@ -159,3 +159,83 @@ class Reducer:
                     view.mul_(inv)
             self.works = []
         self.iterations += 1
+
+
+class NativeReducer:
+    """``backend='b200'``: the counting / ordering / launching lives in the C++ reducer (``csrc/reducer.cu``);
+    this class only forwards stream handles.  Same interface as ``Reducer``."""
+
+    def __init__(self, arena: torch.Tensor, buckets: List[Bucket], param_bucket: List[int], world_size: int, comm,
+                 arena_offset_bytes: int = 0):
+        import ctypes
+        from ctypes import byref, c_float, c_int, c_size_t, c_void_p
+        from ..ops import _lib as L
+        self._L, self._ct = L, ctypes
+        self.arena, self.buckets, self.param_bucket = arena, buckets, param_bucket
+        self.world_size, self.comm = world_size, comm
+        self.require_sync = True
+        self.iterations = 0
+        self.ready_order: List[int] = []
+        self.in_backward = False
+        lib = L.lib()
+        lib.b200_reducer_create.restype = c_void_p
+        n, nb = len(param_bucket), len(buckets)
+        pb = (c_int * n)(*param_bucket)
+        offs = (c_size_t * nb)(*[arena_offset_bytes + b.start * 4 for b in buckets])
+        cnts = (c_size_t * nb)(*[b.numel for b in buckets])
+        cfg = comm.cfg
+        self._h = lib.b200_reducer_create(byref(comm.cs), c_int(n), pb, c_int(nb), offs, cnts, c_int(L.DTYPE_F32),
+                                          c_float(1.0 / world_size), c_int(cfg.max_ctas), c_size_t(cfg.oneshot_max_bytes),
+                                          c_size_t(cfg.nvls_min_bytes if comm.has_nvls else (1 << 62)))
+        if not self._h:
+            raise L.NativeError("b200_reducer_create failed: %s" % lib.b200_last_error().decode())
+        self._h = c_void_p(self._h)
+        self._lib = lib
+        self._comm_stream = c_void_p(comm.comm_stream.cuda_stream)
+
+    def __del__(self):
+        try:
+            self._lib.b200_reducer_destroy(self._h)
+        except Exception:
+            pass
+
+    def prepare_for_backward(self):
+        self._L.check(self._lib.b200_reducer_begin(self._h), "reducer_begin")
+        self.in_backward = True
+        if self.iterations == 0:
+            self.ready_order = []
+
+    def was_written(self, param_id: int) -> bool:
+        return bool(self._lib.b200_reducer_was_ready(self._h, self._ct.c_int(param_id)))
+
+    def _streams(self):
+        from ..ops import streams
+        dev = self.comm.device
+        cur = torch.cuda.current_stream(dev)
+        others = streams.producers(dev)
+        other = self._ct.c_void_p(others[0].cuda_stream) if others else self._ct.c_void_p(0)
+        return self._ct.c_void_p(cur.cuda_stream), other
+
+    def mark_ready(self, param_id: int):
+        if self.iterations == 0:
+            self.ready_order.append(param_id)
+        if not self.require_sync or self.world_size == 1:
+            return
+        cur, other = self._streams()
+        rc = self._lib.b200_reducer_mark_ready(self._h, self._ct.c_int(param_id), cur, other, self._comm_stream)
+        if rc < 0:
+            self._L.check(rc, "reducer_mark_ready")
+        for _ in range(rc):
+            self._L.LAUNCHES[0] += 1
+
+    def finalize(self):
+        self.in_backward = False
+        cur, other = self._streams()
+        self._L.check(self._lib.b200_reducer_finalize(self._h, cur, other, self._comm_stream,
+                                                      self._ct.c_int(int(self.require_sync))), "reducer_finalize")
+        if not getattr(self, "_logged", False) and self.world_size > 1 and self.require_sync:
+            self._logged = True
+            for b in self.buckets:
+                a = self._lib.b200_reducer_bucket_algo(self._h, self._ct.c_int(b.index))
+                self.comm.launch_log.append((self._L.ALGO_NAMES.get(a, "?"), b.numel * 4))
+        self.iterations += 1

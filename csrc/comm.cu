@@ -46,21 +46,43 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
   return t;
 }
 
-// All threads of the CTA must call this.  Orders every earlier memory operation of the CTA before the
-// flag (release, system scope) and every later one after the peers' flags (acquire).
-__device__ __forceinline__ void cta_barrier_all_ranks(const b200_comm& c) {
-  __threadfence_system();
+__device__ __forceinline__ void st_relaxed_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// Per-CTA barrier across all ranks.  All threads of the CTA must call it.  `epoch` is the CTA's barrier
+// counter, loaded once per kernel (barrier_begin) and stored back once (barrier_end).
+//
+// RELEASE = true : this CTA wrote peer memory (pushed / multicast stores) that the peers consume after the
+//                  barrier -> every thread fences at system scope before the flag goes out.
+// RELEASE = false: the barrier only orders "everyone arrived" (start of a collective: the data was written
+//                  by earlier kernels, complete at the kernel boundary) or "everyone finished reading".  Flags
+//                  are relaxed system-scope stores/loads; system-scope MEMBARs cost microseconds each and are
+//                  what dominated small-message latency.
+__device__ __forceinline__ uint32_t barrier_begin(const b200_comm& c) {
+  return reinterpret_cast<uint32_t*>(c.peer[c.rank] + kEpochOff)[blockIdx.x];
+}
+__device__ __forceinline__ void barrier_end(const b200_comm& c, uint32_t epoch) {
+  if (threadIdx.x == 0) reinterpret_cast<uint32_t*>(c.peer[c.rank] + kEpochOff)[blockIdx.x] = epoch;
+}
+template <bool RELEASE>
+__device__ __forceinline__ void cta_barrier_all_ranks(const b200_comm& c, uint32_t& epoch) {
+  if (RELEASE) __threadfence_system();
   __syncthreads();
-  uint32_t* epochs = reinterpret_cast<uint32_t*>(c.peer[c.rank] + kEpochOff);
-  const uint32_t e = epochs[blockIdx.x] + 1;
+  const uint32_t e = ++epoch;
   if (threadIdx.x < c.world) {
     const int r = threadIdx.x;
-    st_release_sys(sig_slot(c.peer[r], e & 1u, blockIdx.x, c.rank), e);
+    st_relaxed_sys(sig_slot(c.peer[r], e & 1u, blockIdx.x, c.rank), e);
     const uint32_t* mine = sig_slot(c.peer[c.rank], e & 1u, blockIdx.x, r);
-    if (ld_acquire_sys(mine) != e) {
+    if (ld_relaxed_sys(mine) != e) {
       const unsigned long long t0 = globaltimer_ns();
       unsigned spins = 0;
-      while (ld_acquire_sys(mine) != e) {
+      while (ld_relaxed_sys(mine) != e) {
         if ((++spins & 0x3ff) == 0 && globaltimer_ns() - t0 > c.timeout_ns) {
           if (c.err_flag) {
             c.err_flag[0] = 1;
@@ -73,7 +95,6 @@ __device__ __forceinline__ void cta_barrier_all_ranks(const b200_comm& c) {
     }
   }
   __syncthreads();
-  if (threadIdx.x == 0) epochs[blockIdx.x] = e;
 }
 
 // ---- 16-byte vector traits -----------------------------------------------------------------------
@@ -157,7 +178,8 @@ template <int DT, int WORLD, int UNROLL>
 __global__ void __launch_bounds__(kThreads, 1)
 allreduce_oneshot_kernel(b200_comm c, size_t offset, char* out, size_t chunks, float scale, int need_mid_barrier) {
   using V = Vec<DT>;
-  cta_barrier_all_ranks(c);  // every peer entered: its gradients for this bucket are final
+  uint32_t epoch = barrier_begin(c);
+  cta_barrier_all_ranks<false>(c, epoch);  // every peer entered: its gradients for this bucket are final
   const size_t per_round = (size_t)gridDim.x * kThreads * UNROLL;
   for (size_t base = (size_t)blockIdx.x * kThreads * UNROLL; base < chunks; base += per_round) {
     float acc[UNROLL][V::kElems];
@@ -178,14 +200,15 @@ allreduce_oneshot_kernel(b200_comm c, size_t offset, char* out, size_t chunks, f
 #pragma unroll
       for (int r = 0; r < WORLD; ++r) V::accumulate(acc[u], raw[r][u]);  // fixed order 0..N-1
     }
-    if (need_mid_barrier) cta_barrier_all_ranks(c);
+    if (need_mid_barrier) cta_barrier_all_ranks<false>(c, epoch);   // all ranks hold this round in registers
 #pragma unroll
     for (int u = 0; u < UNROLL; ++u) {
       const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
       if (idx < chunks) *reinterpret_cast<int4*>(out + idx * 16) = V::pack(acc[u], scale);
     }
   }
-  if (!need_mid_barrier) cta_barrier_all_ranks(c);  // out-of-place: protect the arena from early reuse
+  if (!need_mid_barrier) cta_barrier_all_ranks<false>(c, epoch);  // out-of-place: protect the arena from early reuse
+  barrier_end(c, epoch);
 }
 
 // ---- W2 two-shot (pull-reduce + push-broadcast) and W3 NVLS ---------------------------------------
@@ -197,7 +220,8 @@ allreduce_shard_kernel(b200_comm c, size_t offset, size_t chunks, float scale) {
   const size_t per = (chunks + WORLD - 1) / WORLD;
   const size_t lo = (size_t)c.rank * per;
   const size_t hi = lo + per < chunks ? lo + per : chunks;
-  cta_barrier_all_ranks(c);
+  uint32_t epoch = barrier_begin(c);
+  cta_barrier_all_ranks<false>(c, epoch);
   const size_t per_round = (size_t)gridDim.x * kThreads * UNROLL;
   for (size_t base = lo + (size_t)blockIdx.x * kThreads * UNROLL; base < hi; base += per_round) {
     if constexpr (NVLS) {
@@ -248,12 +272,14 @@ allreduce_shard_kernel(b200_comm c, size_t offset, size_t chunks, float scale) {
       }
     }
   }
-  cta_barrier_all_ranks(c);  // all pushed / multicast stores have landed everywhere
+  cta_barrier_all_ranks<true>(c, epoch);  // all pushed / multicast stores have landed everywhere
+  barrier_end(c, epoch);
 }
 
 // ---- W4 broadcast (pull) --------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, 1) broadcast_kernel(b200_comm c, size_t offset, size_t chunks, int root) {
-  cta_barrier_all_ranks(c);  // root's data is final, receivers' buffers are free
+  uint32_t epoch = barrier_begin(c);
+  cta_barrier_all_ranks<false>(c, epoch);  // root's data is final, receivers' buffers are free
   if (c.rank != root) {
     const char* src = c.peer[root] + offset;
     char* dst = c.peer[c.rank] + offset;
@@ -261,10 +287,15 @@ __global__ void __launch_bounds__(kThreads, 1) broadcast_kernel(b200_comm c, siz
     for (size_t i = (size_t)blockIdx.x * kThreads + threadIdx.x; i < chunks; i += stride)
       *reinterpret_cast<int4*>(dst + i * 16) = ld_peer(src + i * 16);
   }
-  cta_barrier_all_ranks(c);  // root may overwrite again
+  cta_barrier_all_ranks<false>(c, epoch);  // root may overwrite again
+  barrier_end(c, epoch);
 }
 
-__global__ void __launch_bounds__(kThreads, 1) barrier_kernel(b200_comm c) { cta_barrier_all_ranks(c); }
+__global__ void __launch_bounds__(kThreads, 1) barrier_kernel(b200_comm c) {
+  uint32_t epoch = barrier_begin(c);
+  cta_barrier_all_ranks<true>(c, epoch);
+  barrier_end(c, epoch);
+}
 
 template <typename T>
 __global__ void scale_kernel(T* p, size_t n, float scale);

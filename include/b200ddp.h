@@ -80,6 +80,22 @@ int b200_broadcast(const b200_comm* comm, size_t offset, size_t bytes, int root,
 int b200_barrier(const b200_comm* comm, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Gradient reducer (replaces torch's C++ DDP Reducer — …native-cpu.py:141, …smddp-gpu.py:148): ready
+ * counting per bucket, in-order launch of b200_allreduce on the comm stream behind stream events, join at
+ * the end of backward.  Buckets are byte ranges of the symmetric gradient arena.  Stream-ordered only.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct b200_reducer b200_reducer;
+b200_reducer* b200_reducer_create(const b200_comm* comm, int n_params, const int* param_bucket, int n_buckets,
+                                  const size_t* bucket_offset_bytes, const size_t* bucket_count, int dtype,
+                                  float scale, int max_blocks, size_t oneshot_max_bytes, size_t nvls_min_bytes);
+void b200_reducer_destroy(b200_reducer* r);
+int b200_reducer_begin(b200_reducer* r);
+int b200_reducer_was_ready(const b200_reducer* r, int param);
+int b200_reducer_mark_ready(b200_reducer* r, int param, void* producer_stream, void* other_stream, void* comm_stream);
+int b200_reducer_finalize(b200_reducer* r, void* main_stream, void* other_stream, void* comm_stream, int sync_grads);
+int b200_reducer_bucket_algo(const b200_reducer* r, int bucket);
+
+/* ---------------------------------------------------------------------------------------------
  * Optimizers over flat arenas (replace ATen foreach SGD / Adam — …native-cpu.py:144,156;
  * utils_basic.py:96).  p/g/m/v are fp32; shadow (may be NULL) receives the bf16 copy of p.
  * ------------------------------------------------------------------------------------------- */

@@ -41,6 +41,7 @@ def main():
     ap.add_argument("--max-mb", type=int, default=256)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--out", type=str, default="")
+    ap.add_argument("--graph", action="store_true", help="time the all-reduces inside one CUDA graph (no host launch cost)")
     a = ap.parse_args()
     bd.init_process_group(backend="b200")
     rank, world = bd.get_rank(), bd.get_world_size()
@@ -112,10 +113,22 @@ def main():
                 torch.cuda.synchronize()
                 dist.barrier()
                 s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                s.record()
-                for _ in range(a.iters):
-                    comm.all_reduce_arena(off, n, scale=1.0 / world, algo=algo)
-                e.record()
+                if a.graph:
+                    g = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(g):
+                        for _ in range(a.iters):
+                            comm.all_reduce_arena(off, n, scale=1.0 / world, algo=algo)
+                    g.replay()
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    s.record()
+                    g.replay()
+                    e.record()
+                else:
+                    s.record()
+                    for _ in range(a.iters):
+                        comm.all_reduce_arena(off, n, scale=1.0 / world, algo=algo)
+                    e.record()
                 torch.cuda.synchronize()
                 us = bd.max_over_ranks(s.elapsed_time(e) / a.iters * 1e3)
                 row[L.ALGO_NAMES[algo] + "_us"] = us
