@@ -82,6 +82,11 @@ class SymmComm:
             raise RuntimeError("backend 'b200' is a single-node NVSwitch backend: world_size <= %d" % L.MAX_RANKS)
         self.rank, self.world, self.device = rank, world_size, device
         self.cfg = CommConfig()
+        # algorithm thresholds measured on 2 and 8 B200s (profiles/allreduce_sweep.md): one-shot pulls
+        # (N-1) x S per GPU, so its cut-over shrinks with N; with 2 ranks the switch reduction buys nothing
+        if "B200DDP_ONESHOT_MAX_BYTES" not in os.environ and world_size > 1:
+            self.cfg.oneshot_max_bytes = max(64 * 1024, (2 << 20) // (world_size - 1))
+        self.prefer_nvls = world_size > 2 or "B200DDP_NVLS_MIN_BYTES" in os.environ
         self.lib = L.lib()
         dev = device.index if device.index is not None else torch.cuda.current_device()
         self.dev_index = dev
@@ -215,7 +220,7 @@ class SymmComm:
     def pick_algo(self, nbytes: int) -> int:
         if nbytes <= self.cfg.oneshot_max_bytes:
             return L.ALGO_ONESHOT
-        if self.has_nvls and nbytes >= self.cfg.nvls_min_bytes:
+        if self.has_nvls and self.prefer_nvls and nbytes >= self.cfg.nvls_min_bytes:
             return L.ALGO_NVLS
         return L.ALGO_TWOSHOT
 

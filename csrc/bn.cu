@@ -121,8 +121,12 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, size_t rows, int C, const f
     }
   }
   const float tot = cta_reduce_rows(s, q, sm);
-  if (!publish_and_elect(tot, partial, counters)) return;
-  {
+  if (gridDim.x == 1) {
+    // one row block per channel group (small tensors): the CTA total IS the result — skip the scratch
+    // round trips (partial store, fence, ticket atomic, re-load), which cost more than the reduction itself
+    if (threadIdx.x < 2 * kGroup) fin[threadIdx.x >> 6][threadIdx.x & 63] = tot;
+  } else {
+    if (!publish_and_elect(tot, partial, counters)) return;
     const float t = sum_partials(partial);
     if (threadIdx.x < 2 * kGroup) fin[threadIdx.x >> 6][threadIdx.x & 63] = t;
   }
@@ -244,8 +248,11 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     }
   }
   const float tot = cta_reduce_rows(s, q, sm);
-  if (!publish_and_elect(tot, partial, counters)) return;
-  const float t = sum_partials(partial);
+  float t = tot;
+  if (gridDim.x > 1) {
+    if (!publish_and_elect(tot, partial, counters)) return;
+    t = sum_partials(partial);
+  }
   if (threadIdx.x < 2 * kGroup) {
     const int which = threadIdx.x >> 6, ch = blockIdx.y * kGroup + (threadIdx.x & 63);
     if (ch < C) {
@@ -304,7 +311,7 @@ dim3 bn_grid(size_t rows, int C, int per_sm) {
 // Reductions: few, fat CTAs (>= 256 rows each, <= 128 row blocks) so the electing CTA's final sum is short.
 dim3 bn_reduce_grid(size_t rows, int C) {
   const int cg = (C + kGroup - 1) / kGroup;
-  size_t rb = rows / 256;
+  size_t rb = rows <= 2048 ? 1 : rows / 256;   // <= 2048 rows: one CTA per channel group, no scratch traffic
   if (rb > 128) rb = 128;
   if (rb < 1) rb = 1;
   return dim3((unsigned)rb, (unsigned)cg, 1);

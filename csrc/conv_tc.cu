@@ -48,6 +48,7 @@ constexpr int STAGES = 6;
 constexpr int LAG = 4;                 // cp.async groups kept in flight behind the newest one
 constexpr int PRODUCERS = 128;
 constexpr int THREADS = PRODUCERS + 32;
+long long* g_prof = nullptr;           // b200_conv_set_profile_buffer
 bool g_split_k = true;                 // b200_conv_set_split_k(0) pins FWD/DGRAD to one CTA per tile (reproducibility checks)
 
 struct ConvParams {
@@ -65,6 +66,7 @@ struct ConvParams {
   uint32_t kb_per_split;     // virtual k-blocks per grid.z slice
   uint32_t cpt;              // k-blocks per filter tap (0: no tap skipping, virtual == real)
   uint32_t a_tma, b_tma;     // operand staged by TMA (plain 2-D matrix) instead of the cp.async gather
+  long long* prof;           // optional: CTA (0,0,0) drops clock64() stamps of its phases here (tuning aid)
   unsigned long long tapmask;  // bit t set: tap t can touch a real pixel somewhere in the tensor
   uint8_t tap_list[64];      // the set bits of tapmask, ascending
   FastDiv div_c, div_s, div_kc, div_wo, div_ho, div_w, div_h, div_cpt;
@@ -77,7 +79,7 @@ struct Cfg {
   static constexpr int A_BYTES = BM * BK * 2;          // 16 KiB either way
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 2048 /*row info*/;
 };
 
 __device__ __forceinline__ uint32_t virt2kb(const ConvParams& p, uint32_t v) {
@@ -86,38 +88,35 @@ __device__ __forceinline__ uint32_t virt2kb(const ConvParams& p, uint32_t v) {
   return (uint32_t)p.tap_list[q] * p.cpt + (v - q * p.cpt);
 }
 
-// Write NCOLS accumulator columns [nn0, nn0+NCOLS) of GEMM row m.  FWD: +bias, ReLU, bf16.  DGRAD: bf16.
-// WGRAD: fp32 red.add into the gradient arena.
+// Write NCOLS accumulator columns [nn0, nn0+NCOLS) of GEMM row m, 8 columns (one 16-byte bf16 vector) at a
+// time; gemm_n is a multiple of 8 in every mode.  FWD: +bias, ReLU, bf16.  DGRAD: bf16.  WGRAD: fp32 red.add
+// into the gradient arena.  Kept small on purpose: a tile runs this code once, so its size is fetch latency.
 template <int MODE, int NCOLS>
 __device__ __forceinline__ void epilogue_store(const ConvParams& p, uint32_t m, uint32_t nn0, float* f) {
-  if (m >= p.gemm_m || nn0 >= p.gemm_n) return;
-  if (MODE == MODE_WGRAD) {
-    float* dst = reinterpret_cast<float*>(p.out) + (size_t)m * p.gemm_n + nn0;
-    if (nn0 + NCOLS <= p.gemm_n) {
+  if (m >= p.gemm_m) return;
 #pragma unroll
-      for (int q = 0; q < NCOLS / 4; ++q)
-        asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + 4 * q), "f"(f[4 * q]), "f"(f[4 * q + 1]),
-                     "f"(f[4 * q + 2]), "f"(f[4 * q + 3])
-                     : "memory");
+  for (int q = 0; q < NCOLS / 8; ++q) {
+    const uint32_t nn = nn0 + 8 * q;
+    if (nn >= p.gemm_n) break;
+    float* v = f + 8 * q;
+    if (MODE == MODE_WGRAD) {
+      float* dst = reinterpret_cast<float*>(p.out) + (size_t)m * p.gemm_n + nn;
+      asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst), "f"(v[0]), "f"(v[1]), "f"(v[2]), "f"(v[3]) : "memory");
+      asm volatile("red.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(dst + 4), "f"(v[4]), "f"(v[5]), "f"(v[6]), "f"(v[7]) : "memory");
     } else {
-      for (int q = 0; q < NCOLS; ++q)
-        if (nn0 + q < p.gemm_n) atomicAdd(dst + q, f[q]);
-    }
-  } else {
-    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.gemm_n + nn0;
-    if (MODE == MODE_FWD) {
+      if (MODE == MODE_FWD) {
+        if (p.bias != nullptr) {
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + nn));
+          const float4 b1 = __ldg(reinterpret_cast<const float4*>(p.bias + nn) + 1);
+          v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+          v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+        }
+        if (p.relu) {
 #pragma unroll
-      for (int q = 0; q < NCOLS; ++q) {
-        if (p.bias != nullptr && nn0 + q < p.gemm_n) f[q] += __ldg(p.bias + nn0 + q);
-        if (p.relu) f[q] = fmaxf(f[q], 0.f);
+          for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
+        }
       }
-    }
-    if (nn0 + NCOLS <= p.gemm_n) {
-#pragma unroll
-      for (int q = 0; q < NCOLS / 8; ++q) *reinterpret_cast<bf16x8*>(dst + 8 * q) = float_to_bf16x8(f + 8 * q);
-    } else {
-      for (int q = 0; q < NCOLS; ++q)
-        if (nn0 + q < p.gemm_n) dst[q] = __float2bfloat16(f[q]);
+      *reinterpret_cast<bf16x8*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.gemm_n + nn) = float_to_bf16x8(v);
     }
   }
 }
@@ -143,8 +142,13 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  const __nv_bfloat16** s_rowbase = reinterpret_cast<const __nv_bfloat16**>(smem + STAGES * C::STAGE_BYTES + 256);
+  unsigned long long* s_rowmask = reinterpret_cast<unsigned long long*>(smem + STAGES * C::STAGE_BYTES + 256 + 1024);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const bool prof = p.prof != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+#define STAMP(i, t) do { if (prof && tid == (t)) p.prof[i] = clock64(); } while (0)
+  STAMP(0, 0);
   const uint32_t v_begin = blockIdx.z * p.kb_per_split;
   const uint32_t v_end = min(p.nvk, v_begin + p.kb_per_split);
   const uint32_t nkb = v_end > v_begin ? v_end - v_begin : 0;
@@ -165,6 +169,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  STAMP(1, 0);
 
   if (warp < 4) {
     if (nkb > 0) {
@@ -172,28 +177,55 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
       const uint32_t smem_base = smem_u32(smem);
       // K-major A (FWD/DGRAD): thread owns chunk column tid&7 of rows (tid>>3) + 16*i, i<8
       // MN-major A (WGRAD): 16 chunks per K row: column tid&15, rows (tid>>4) + 8*i, i<8
-      int a_n[8], a_h[8], a_w[8];   // FWD: (n, ho*st-pad, wo*st-pad); DGRAD: (n, h+pad, w+pad); n=-1: row out of range
-      if (MODE != MODE_WGRAD) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const uint32_t m = m0 + (tid >> 3) + 16 * i;
+      // Per row: a base pointer and a bit mask of the filter taps that land on a real pixel, computed once per
+      // tile by ONE thread per row (through shared memory).  In the K loop an A chunk is then
+      // `rowbase[i] + tap_offset + channel` guarded by one bit test.
+      //   FWD   base = &x[n, ho*st-pad, wo*st-pad, 0],   tap (r,s) adds  (r*W + s)*C
+      //   DGRAD base = &dy[n, (h+pad)>>sh, (w+pad)>>sh, 0], tap (r,s) subtracts ((r>>sh)*Wo + (s>>sh))*Kc, sh = stride==2;
+      //         a tap is live when (h+pad-r), (w+pad-s) are multiples of the stride and inside the output map.
+      const __nv_bfloat16* rowbase[8];
+      unsigned long long rowmask[8];
+      if (MODE != MODE_WGRAD && !p.a_tma) {
+        const int sh = (p.stride == 2) ? 1 : 0;
+        {
+          const uint32_t m = m0 + tid;                      // tid < 128: this thread's row
+          const __nv_bfloat16* base = (MODE == MODE_FWD) ? p.x : p.dy;
+          unsigned long long mask = 0ull;
           if (m < p.gemm_m) {
+            int h0, w0, hlim, wlim;
             if (MODE == MODE_FWD) {
               const uint32_t t = fdiv(m, p.div_wo), wo = m - t * p.Wo;
               const uint32_t n = fdiv(t, p.div_ho), ho = t - n * p.Ho;
-              a_n[i] = (int)n;
-              a_h[i] = (int)ho * p.stride - p.pad;
-              a_w[i] = (int)wo * p.stride - p.pad;
+              h0 = (int)ho * p.stride - p.pad; w0 = (int)wo * p.stride - p.pad; hlim = p.H; wlim = p.W;
+              base = p.x + (((long long)n * p.H + h0) * p.W + w0) * p.C;
             } else {
               const uint32_t t = fdiv(m, p.div_w), w = m - t * p.W;
               const uint32_t n = fdiv(t, p.div_h), h = t - n * p.H;
-              a_n[i] = (int)n;
-              a_h[i] = (int)h + p.pad;
-              a_w[i] = (int)w + p.pad;
+              h0 = (int)h + p.pad; w0 = (int)w + p.pad; hlim = p.Ho; wlim = p.Wo;
+              base = p.dy + (((long long)n * p.Ho + (h0 >> sh)) * p.Wo + (w0 >> sh)) * p.Kc;
             }
-          } else {
-            a_n[i] = -1; a_h[i] = 0; a_w[i] = 0;
+            unsigned long long sbits = 0ull;
+#pragma unroll 1
+            for (int s2 = 0; s2 < p.S; ++s2) {
+              const int wn = (MODE == MODE_FWD) ? w0 + s2 : w0 - s2;
+              const bool ok = (MODE == MODE_FWD) ? ((unsigned)wn < (unsigned)wlim) : (wn >= 0 && (wn & sh) == 0 && (wn >> sh) < wlim);
+              if (ok) sbits |= 1ull << s2;
+            }
+#pragma unroll 1
+            for (int r = 0; r < p.R; ++r) {
+              const int hn = (MODE == MODE_FWD) ? h0 + r : h0 - r;
+              const bool ok = (MODE == MODE_FWD) ? ((unsigned)hn < (unsigned)hlim) : (hn >= 0 && (hn & sh) == 0 && (hn >> sh) < hlim);
+              if (ok) mask |= sbits << (r * p.S);
+            }
           }
+          s_rowbase[tid] = base;
+          s_rowmask[tid] = mask;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          rowbase[i] = s_rowbase[(tid >> 3) + 16 * i];
+          rowmask[i] = s_rowmask[(tid >> 3) + 16 * i];
         }
       }
       // WGRAD B: chunk column -> (r, s, ci) is fixed for the whole tile
@@ -225,31 +257,21 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
           const uint32_t cdim = (MODE == MODE_FWD) ? (uint32_t)p.C : (uint32_t)p.Kc;
           const uint32_t tap = fdiv(k, MODE == MODE_FWD ? p.div_c : p.div_kc);
           const int ch = (int)(k - tap * cdim);
-          const int r = (int)fdiv(tap, p.div_s), s = (int)tap - r * p.S;
+          const int r = (int)fdiv(tap, p.div_s), s2 = (int)tap - r * p.S;
+          long long off;     // same for every row of the tile
+          if (MODE == MODE_FWD) {
+            off = ((long long)r * p.W + s2) * p.C + ch;
+          } else {
+            const int sh = (p.stride == 2) ? 1 : 0;
+            off = -((long long)(r >> sh) * p.Wo + (s2 >> sh)) * p.Kc + ch;
+          }
+          const unsigned long long bit = k_ok ? (1ull << (tap & 63u)) : 0ull;
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const uint32_t row = (tid >> 3) + 16 * i;
-            bool ok = k_ok && a_n[i] >= 0;
-            const __nv_bfloat16* src = (MODE == MODE_FWD) ? p.x : p.dy;
-            if (MODE == MODE_FWD) {
-              const int h = a_h[i] + r, w = a_w[i] + s;
-              ok = ok && h >= 0 && h < p.H && w >= 0 && w < p.W;
-              if (ok) src = p.x + ((((size_t)a_n[i] * p.H + h) * p.W + w) * p.C + ch);
-            } else {
-              const int hn = a_h[i] - r, wn = a_w[i] - s;   // = ho*stride, wo*stride
-              int ho = hn, wo = wn;
-              bool div_ok = hn >= 0 && wn >= 0;
-              if (p.stride == 2) {
-                ho = hn >> 1; wo = wn >> 1;
-                div_ok = div_ok && ((hn | wn) & 1) == 0;
-              } else if (p.stride != 1) {
-                ho = hn / p.stride; wo = wn / p.stride;
-                div_ok = div_ok && (ho * p.stride == hn) && (wo * p.stride == wn);
-              }
-              ok = ok && div_ok && ho < p.Ho && wo < p.Wo;
-              if (ok) src = p.dy + ((((size_t)a_n[i] * p.Ho + ho) * p.Wo + wo) * p.Kc + ch);
-            }
-            cp_async16(sa + swz(row, j), src, ok);
+            const bool ok = (rowmask[i] & bit) != 0ull;
+            // the dummy source of a zero-filled chunk must be a mapped address: rowbase may point before the tensor
+            cp_async16(sa + swz(row, j), ok ? (rowbase[i] + off) : (MODE == MODE_FWD ? p.x : p.dy), ok);
           }
         } else {  // WGRAD A^T: rows are positions, 16 chunks (128 co) per row
           const uint32_t c = tid & 15;
@@ -347,8 +369,10 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
         const uint32_t first = nkb > LAG ? nkb - LAG : 0;
         for (uint32_t it = first; it < nkb; ++it) mbar_arrive(&full_bar[it % STAGES]);
       }
+      STAMP(2, 0);     // all loads issued and landed
       mbar_wait(tmem_full, 0);
       tc_fence_after();
+      STAMP(3, 0);     // accumulator complete
     }
 
     // =============================== EPILOGUE (TMEM -> registers -> global) ===============================
@@ -408,10 +432,12 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
       if (it + 1 == nkb) umma_commit(tmem_full);  // accumulator complete
     }
   }
+  STAMP(4, 0);         // epilogue phase 1 done (direct store, or partial staged)
   if (ZC > 1) {
     // ... then every CTA reduces its BN/ZC column slice over all peers through distributed shared memory
     // (ld.shared::cluster) and runs the epilogue for that slice.  No atomics, no global scratch.
     cluster_sync_all();
+    STAMP(5, 0);
     if (warp < 4) {
       constexpr int SLICE = BN / ZC;
       const uint32_t rank = cluster_ctarank();
@@ -421,7 +447,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
       float f[SLICE];
 #pragma unroll
       for (int q = 0; q < SLICE; ++q) f[q] = 0.f;
-#pragma unroll 1
+#pragma unroll 2
       for (uint32_t z = 0; z < (uint32_t)ZC; ++z) {
         const uint32_t base = dsmem_addr(stage_u32 + ((rank * SLICE) * BM + row) * 4u, z);
 #pragma unroll
@@ -429,7 +455,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
       }
       if (MODE != MODE_WGRAD || p.nvk > 0) epilogue_store<MODE, SLICE>(p, m, n0 + rank * SLICE, f);
     }
-    cluster_sync_all();      // nobody leaves while a peer may still read its shared memory
+    STAMP(6, 0);
+    cluster_sync_relaxed();  // nobody leaves while a peer may still read its shared memory (no memory ordering needed)
   }
   tc_fence_before();
   __syncthreads();
@@ -437,6 +464,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
     __syncwarp();
     tmem_dealloc(tmem_base, BN);
   }
+  STAMP(7, 0);
+#undef STAMP
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -516,11 +545,13 @@ int fill_common(ConvParams& p, const b200_conv_geom* g) {
   B200_REQUIRE(g->C % 8 == 0 && g->K % 8 == 0, "channel counts must be multiples of 8 (16-byte gathers)");
   B200_REQUIRE(g->stride >= 1 && g->R >= 1 && g->S >= 1 && g->N >= 1, "bad geometry");
   memset(&p, 0, sizeof(p));
+  p.prof = g_prof;
   p.N = g->N; p.H = g->H; p.W = g->W; p.C = g->C;
   p.Kc = g->K; p.R = g->R; p.S = g->S; p.stride = g->stride; p.pad = g->pad;
   p.Ho = (g->H + 2 * g->pad - g->R) / g->stride + 1;
   p.Wo = (g->W + 2 * g->pad - g->S) / g->stride + 1;
   B200_REQUIRE(p.Ho >= 1 && p.Wo >= 1, "empty output");
+  B200_REQUIRE(g->R * g->S <= 64, "filters larger than 64 taps are not supported");
   B200_REQUIRE((size_t)g->N * g->H * g->W < (1ull << 31) && (size_t)g->N * p.Ho * p.Wo < (1ull << 31), "tensor too large for 32-bit tile indices");
   p.div_c = make_fastdiv(p.C); p.div_s = make_fastdiv(p.S); p.div_kc = make_fastdiv(p.Kc);
   p.div_wo = make_fastdiv(p.Wo); p.div_ho = make_fastdiv(p.Ho);
@@ -598,6 +629,11 @@ uint32_t plan_cluster(ConvParams& p, uint32_t tiles) {
 
 }  // namespace
 
+extern "C" int b200_conv_set_profile_buffer(long long* dev_buf8) {
+  g_prof = dev_buf8;
+  return 0;
+}
+
 extern "C" int b200_conv_set_split_k(int enabled) {
   g_split_k = enabled != 0;
   return 0;
@@ -632,6 +668,7 @@ extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b2
   int rc = fill_common(p, g);
   if (rc) return rc;
   B200_REQUIRE(dy && w && dx, "null tensor");
+  B200_REQUIRE(p.stride <= 2, "dgrad supports stride 1 and 2");
   p.dy = (const __nv_bfloat16*)dy; p.w = (const __nv_bfloat16*)w; p.out = dx;
   p.gemm_m = (uint32_t)p.N * p.H * p.W; p.gemm_n = p.C; p.gemm_k = (uint32_t)p.R * p.S * p.Kc;
   plan_k(p, p.Kc);

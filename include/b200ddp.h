@@ -189,6 +189,8 @@ typedef struct b200_conv_geom {
 /* Small problems split K over a thread-block cluster (DSMEM reduction; no scratch).  b200_conv_set_split_k(0)
  * pins fwd/dgrad to one CTA per tile. */
 int b200_conv_set_split_k(int enabled);
+/* Tuning aid: when non-NULL, CTA (0,0,0) of every conv launch writes 8 clock64() phase stamps there. */
+int b200_conv_set_profile_buffer(long long* dev_buf8);
 int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g, int relu,
                   void* stream);
 int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream);
