@@ -220,11 +220,15 @@ def linear(x, weight, bias=None, relu=False, nhwc_from=None):
 class _BatchNormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu):
-        if training:
-            stat = nv.bn_stats(x, gamma.detach(), beta.detach(), eps, momentum, running_mean, running_var)
+        rows = x.numel() // x.shape[1]
+        if training and rows <= nv.BN_SMALL_ROWS:
+            y, stat = nv.bn_fwd_fused(x, residual, gamma.detach(), beta.detach(), eps, momentum, running_mean, running_var, relu)
         else:
-            stat = nv.bn_eval_prep(gamma.detach(), beta.detach(), running_mean, running_var, eps)
-        y = nv.bn_apply(x, residual, stat, relu)
+            if training:
+                stat = nv.bn_stats(x, gamma.detach(), beta.detach(), eps, momentum, running_mean, running_var)
+            else:
+                stat = nv.bn_eval_prep(gamma.detach(), beta.detach(), running_mean, running_var, eps)
+            y = nv.bn_apply(x, residual, stat, relu)
         ctx.save_for_backward(x, y if relu else None, stat)
         ctx.meta = (gamma, beta, relu, residual is not None, training)
         return y
@@ -238,12 +242,20 @@ class _BatchNormFn(torch.autograd.Function):
         dy = nv.to_cl(dy) if dy.dim() == 4 else dy.contiguous()
         gs, bs = getattr(gamma, "_b200_sink", None), getattr(beta, "_b200_sink", None)
         C = gamma.numel()
+        small = (x.numel() // x.shape[1]) <= nv.BN_SMALL_ROWS
         if gs is not None and bs is not None:
             # the arena is zeroed by the optimizer, so beta_accum=1 both overwrites and accumulates correctly
-            dx, dres, _ = nv.bn_bwd(dy, x, y, stat, relu, has_res, gs.flat[:C], bs.flat[:C], 1.0)
+            if small:
+                dx, dres = nv.bn_bwd_fused(dy, x, y, stat, relu, has_res, gs.flat[:C], bs.flat[:C], 1.0)
+            else:
+                dx, dres, _ = nv.bn_bwd(dy, x, y, stat, relu, has_res, gs.flat[:C], bs.flat[:C], 1.0)
             gs.done()
             bs.done()
             return dx, dres, None, None, None, None, None, None, None, None
+        if small:
+            dg, db = torch.zeros(C, device=x.device), torch.zeros(C, device=x.device)
+            dx, dres = nv.bn_bwd_fused(dy, x, y, stat, relu, has_res, dg, db, 0.0)
+            return dx, dres, dg, db, None, None, None, None, None, None
         dx, dres, sums = nv.bn_bwd(dy, x, y, stat, relu, has_res)
         return dx, dres, sums[1].clone(), sums[0].clone(), None, None, None, None, None, None
 

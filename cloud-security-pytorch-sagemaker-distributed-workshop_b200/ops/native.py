@@ -181,6 +181,33 @@ def bn_apply(x: torch.Tensor, residual: Optional[torch.Tensor], stat: torch.Tens
     return y
 
 
+# The single-launch BN kernels accept up to b200_bn_small_rows() = 2048 rows, but one CTA per channel group only
+# wins while the per-thread row loop is short: measured on B200, 1024 rows (resnet18 layer3 at batch 256) is already
+# slower than the two multi-CTA launches.  B200DDP_BN_FUSED_ROWS overrides.
+BN_SMALL_ROWS = int(__import__("os").environ.get("B200DDP_BN_FUSED_ROWS", "256"))
+
+
+def bn_fwd_fused(x, residual, gamma, beta, eps, momentum, running_mean, running_var, relu: bool):
+    """Training-mode BN(+residual)(+ReLU) in ONE launch for small tensors. Returns (y, stat)."""
+    rows, C = _rows_c(x)
+    stat = torch.empty((4, C), dtype=torch.float32, device=x.device)
+    y = torch.empty_like(x)
+    L.check(L.lib().b200_bn_fwd_fused(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(gamma), L.ptr(beta),
+                                      c_float(eps), c_float(momentum), L.ptr(stat), L.ptr(running_mean), L.ptr(running_var),
+                                      c_int(int(relu)), L.stream_ptr()), "bn_fwd_fused")
+    return y, stat
+
+
+def bn_bwd_fused(dy, x, y, stat, relu: bool, want_dres: bool, dgamma=None, dbeta=None, beta_accum: float = 0.0):
+    rows, C = _rows_c(x)
+    dx = torch.empty_like(x)
+    dres = torch.empty_like(x) if want_dres else None
+    L.check(L.lib().b200_bn_bwd_fused(L.ptr(dy), L.ptr(x), L.ptr(y), L.ptr(dx), L.ptr(dres), c_size_t(rows), c_int(C),
+                                      L.ptr(stat), c_int(int(relu)), L.ptr(dgamma), L.ptr(dbeta), c_float(beta_accum),
+                                      L.stream_ptr()), "bn_bwd_fused")
+    return dx, dres
+
+
 def bn_bwd(dy, x, y, stat, relu: bool, want_dres: bool, dgamma=None, dbeta=None, beta_accum: float = 0.0):
     """Returns (dx, dres, sums[2,C]); dgamma/dbeta (if given) receive beta_accum*old + new."""
     rows, C = _rows_c(x)

@@ -298,6 +298,152 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   }
 }
 
+// ---- small tensors (rows <= kSmallRows): one CTA per channel group sees every row, so statistics + apply
+// (forward) and reduce + apply (backward) are ONE launch each; the second pass over the rows hits L2.
+constexpr size_t kSmallRows = 2048;
+
+template <bool kRelu, bool kRes>
+__global__ void __launch_bounds__(kThreads)
+bn_fwd_small_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
+                    __nv_bfloat16* __restrict__ y, size_t rows, int C, const float* __restrict__ gamma,
+                    const float* __restrict__ beta, float eps, float momentum, float* __restrict__ stat,
+                    float* __restrict__ running_mean, float* __restrict__ running_var) {
+  __shared__ float sm[2][kRL][kGroup];
+  __shared__ float fin[2][kGroup];
+  const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
+  const int c = blockIdx.y * kGroup + v * 8;
+  float s[8], q[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
+  if (c < C) {
+#pragma unroll 2
+    for (size_t r = rl; r < rows; r += kRL) {
+      float f[8];
+      bf16x8_to_float(ld_vec(x + r * C + c), f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        s[k] += f[k];
+        q[k] = fmaf(f[k], f[k], q[k]);
+      }
+    }
+  }
+  const float tot = cta_reduce_rows(s, q, sm);
+  if (threadIdx.x < 2 * kGroup) fin[threadIdx.x >> 6][threadIdx.x & 63] = tot;
+  __syncthreads();
+  if (threadIdx.x < kGroup) {
+    const int ch = blockIdx.y * kGroup + threadIdx.x;
+    if (ch < C) {
+      const float inv_n = 1.f / (float)rows;
+      const float mean = fin[0][threadIdx.x] * inv_n;
+      const float var = fmaxf(fin[1][threadIdx.x] * inv_n - mean * mean, 0.f);
+      const float rstd = rsqrtf(var + eps);
+      const float sc = gamma[ch] * rstd;
+      stat[ch] = mean;
+      stat[C + ch] = rstd;
+      stat[2 * C + ch] = sc;
+      stat[3 * C + ch] = beta[ch] - mean * sc;
+      fin[0][threadIdx.x] = sc;
+      fin[1][threadIdx.x] = beta[ch] - mean * sc;
+      if (running_mean != nullptr) {
+        const float unbiased = rows > 1 ? var * (float)rows / (float)(rows - 1) : var;
+        running_mean[ch] = (1.f - momentum) * running_mean[ch] + momentum * mean;
+        running_var[ch] = (1.f - momentum) * running_var[ch] + momentum * unbiased;
+      }
+    }
+  }
+  __syncthreads();
+  if (c >= C) return;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sc[k] = fin[0][v * 8 + k];
+    sh[k] = fin[1][v * 8 + k];
+  }
+#pragma unroll 2
+  for (size_t r = rl; r < rows; r += kRL) {
+    float f[8], rr[8];
+    bf16x8_to_float(ld_vec(x + r * C + c), f);
+    if (kRes) bf16x8_to_float(ld_vec(res + r * C + c), rr);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float o = fmaf(f[k], sc[k], sh[k]);
+      if (kRes) o += rr[k];
+      if (kRelu) o = fmaxf(o, 0.f);
+      f[k] = o;
+    }
+    st_vec(y + r * C + c, float_to_bf16x8(f));
+  }
+}
+
+template <bool kRelu, bool kRes>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_small_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx,
+                    __nv_bfloat16* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
+                    float* __restrict__ dgamma, float* __restrict__ dbeta, float beta_accum) {
+  __shared__ float sm[2][kRL][kGroup];
+  __shared__ float fin[2][kGroup];
+  const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
+  const int c = blockIdx.y * kGroup + v * 8;
+  float s[8], q[8], mean[8], rstd[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = q[k] = mean[k] = rstd[k] = 0.f;
+  if (c < C) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      mean[k] = stat[c + k];
+      rstd[k] = stat[C + c + k];
+    }
+#pragma unroll 2
+    for (size_t r = rl; r < rows; r += kRL) {
+      float g[8], xv[8], yv[8];
+      bf16x8_to_float(ld_vec(dy + r * C + c), g);
+      bf16x8_to_float(ld_vec(x + r * C + c), xv);
+      if (kRelu) bf16x8_to_float(ld_vec(y + r * C + c), yv);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float gg = (kRelu && !(yv[k] > 0.f)) ? 0.f : g[k];
+        s[k] += gg;
+        q[k] = fmaf(gg, (xv[k] - mean[k]) * rstd[k], q[k]);
+      }
+    }
+  }
+  const float tot = cta_reduce_rows(s, q, sm);
+  if (threadIdx.x < 2 * kGroup) {
+    const int which = threadIdx.x >> 6, ch = blockIdx.y * kGroup + (threadIdx.x & 63);
+    fin[which][threadIdx.x & 63] = tot;
+    if (ch < C) {
+      float* dst = which == 0 ? dbeta : dgamma;
+      if (dst != nullptr) dst[ch] = beta_accum != 0.f ? fmaf(beta_accum, dst[ch], tot) : tot;
+    }
+  }
+  __syncthreads();
+  if (c >= C) return;
+  const float inv_n = 1.f / (float)rows;
+  float a[8], m1[8], m2[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    a[k] = stat[2 * C + c + k];
+    m1[k] = fin[0][v * 8 + k] * inv_n;
+    m2[k] = fin[1][v * 8 + k] * inv_n;
+  }
+#pragma unroll 2
+  for (size_t r = rl; r < rows; r += kRL) {
+    float g[8], xv[8], yv[8];
+    bf16x8_to_float(ld_vec(dy + r * C + c), g);
+    bf16x8_to_float(ld_vec(x + r * C + c), xv);
+    if (kRelu) bf16x8_to_float(ld_vec(y + r * C + c), yv);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float gg = (kRelu && !(yv[k] > 0.f)) ? 0.f : g[k];
+      g[k] = gg;
+      xv[k] = a[k] * (gg - m1[k] - (xv[k] - mean[k]) * rstd[k] * m2[k]);
+    }
+    st_vec(dx + r * C + c, float_to_bf16x8(xv));
+    if (kRes) st_vec(dres + r * C + c, float_to_bf16x8(g));
+  }
+}
+
 dim3 bn_grid(size_t rows, int C, int per_sm) {
   const int cg = (C + kGroup - 1) / kGroup;
   size_t rb = (rows + kRL - 1) / kRL;
@@ -470,6 +616,49 @@ extern "C" int b200_bn_stats_noalloc(const void* x_bf16, size_t rows, int C, con
   bn_stats_kernel<<<g, kThreads, 0, s>>>((const __nv_bfloat16*)x_bf16, rows, C, gamma, beta, eps, momentum, stat,
                                          running_mean, running_var, (float*)(scratch + kCounterBytes),
                                          (unsigned*)scratch);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" size_t b200_bn_small_rows(void) { return kSmallRows; }
+
+extern "C" int b200_bn_fwd_fused(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C,
+                                 const float* gamma, const float* beta, float eps, float momentum, float* stat,
+                                 float* running_mean, float* running_var, int relu, void* stream) {
+  B200_REQUIRE(x_bf16 && y_bf16 && gamma && beta && stat, "null argument");
+  B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
+  B200_REQUIRE(rows <= kSmallRows, "fused BN forward handles at most b200_bn_small_rows() rows; use bn_stats + bn_apply");
+  dim3 g(1, (C + kGroup - 1) / kGroup, 1);
+  cudaStream_t s = (cudaStream_t)stream;
+  const __nv_bfloat16 *x = (const __nv_bfloat16*)x_bf16, *r = (const __nv_bfloat16*)residual_bf16;
+  __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
+#define B200_BNF(R, S) bn_fwd_small_kernel<R, S><<<g, kThreads, 0, s>>>(x, r, y, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var)
+  if (relu && r) B200_BNF(true, true);
+  else if (relu) B200_BNF(true, false);
+  else if (r) B200_BNF(false, true);
+  else B200_BNF(false, false);
+#undef B200_BNF
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+extern "C" int b200_bn_bwd_fused(const void* dy_bf16, const void* x_bf16, const void* y_bf16, void* dx_bf16,
+                                 void* dres_bf16, size_t rows, int C, const float* stat, int relu, float* dgamma,
+                                 float* dbeta, float beta_accum, void* stream) {
+  B200_REQUIRE(dy_bf16 && x_bf16 && dx_bf16 && stat, "null argument");
+  B200_REQUIRE(!relu || y_bf16, "relu mask needs y");
+  B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
+  B200_REQUIRE(rows <= kSmallRows, "fused BN backward handles at most b200_bn_small_rows() rows");
+  dim3 g(1, (C + kGroup - 1) / kGroup, 1);
+  cudaStream_t s = (cudaStream_t)stream;
+  const __nv_bfloat16 *dy = (const __nv_bfloat16*)dy_bf16, *x = (const __nv_bfloat16*)x_bf16, *y = (const __nv_bfloat16*)y_bf16;
+  __nv_bfloat16 *dx = (__nv_bfloat16*)dx_bf16, *dr = (__nv_bfloat16*)dres_bf16;
+#define B200_BNB(R, S) bn_bwd_small_kernel<R, S><<<g, kThreads, 0, s>>>(dy, x, y, dx, dr, rows, C, stat, dgamma, dbeta, beta_accum)
+  if (relu && dr) B200_BNB(true, true);
+  else if (relu) B200_BNB(true, false);
+  else if (dr) B200_BNB(false, true);
+  else B200_BNB(false, false);
+#undef B200_BNB
   B200_CHECK_LAUNCH();
   return 0;
 }

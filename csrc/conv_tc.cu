@@ -308,15 +308,30 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
           const uint32_t c = tid % CPR;
           const uint32_t ci = n0 + c * 8;
           const bool ci_ok = ci < p.gemm_n;
+          if (p.cpt != 0 || (p.Kc % BK) == 0) {
+            // Cout multiple of 64: the 64 rows of this k-block share one tap and walk consecutive co
+            const uint32_t k0 = kb * BK;
+            const uint32_t tap = fdiv(k0, p.div_kc);
+            const uint32_t co0 = k0 - tap * p.Kc;
+            const size_t row_stride = (size_t)(p.R * p.S) * p.C;
+            const __nv_bfloat16* base = p.w + ((size_t)co0 * (p.R * p.S) + tap) * p.C + ci;
+            const bool blk_ok = ci_ok && k0 < p.gemm_k;
 #pragma unroll
-          for (int i = 0; i < BK / RPP; ++i) {
-            const uint32_t row = (tid / CPR) + RPP * i;
-            const uint32_t k = kb * BK + row;
-            const bool ok = ci_ok && k < p.gemm_k;
-            const uint32_t tap = fdiv(k, p.div_kc);
-            const uint32_t co = k - tap * p.Kc;
-            const __nv_bfloat16* src = ok ? p.w + (((size_t)co * (p.R * p.S) + tap) * p.C + ci) : p.w;
-            cp_async16(sb + (c >> 3) * (BK * 128) + swz(row, c & 7), src, ok);
+            for (int i = 0; i < BK / RPP; ++i) {
+              const uint32_t row = (tid / CPR) + RPP * i;
+              cp_async16(sb + (c >> 3) * (BK * 128) + swz(row, c & 7), blk_ok ? base + row * row_stride : p.w, blk_ok);
+            }
+          } else {
+#pragma unroll 1
+            for (int i = 0; i < BK / RPP; ++i) {
+              const uint32_t row = (tid / CPR) + RPP * i;
+              const uint32_t k = kb * BK + row;
+              const bool ok = ci_ok && k < p.gemm_k;
+              const uint32_t tap = fdiv(k, p.div_kc);
+              const uint32_t co = k - tap * p.Kc;
+              const __nv_bfloat16* src = ok ? p.w + (((size_t)co * (p.R * p.S) + tap) * p.C + ci) : p.w;
+              cp_async16(sb + (c >> 3) * (BK * 128) + swz(row, c & 7), src, ok);
+            }
           }
         } else {  // WGRAD B^T: rows are positions, chunk column fixed (r,s,ci)
           constexpr int CPR = BN / 8;

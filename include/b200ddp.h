@@ -157,6 +157,14 @@ int b200_bn_bwd_reduce(const void* dy_bf16, const void* x_bf16, const void* y_bf
 int b200_bn_bwd_apply(const void* dy_bf16, const void* x_bf16, const void* y_bf16, void* dx_bf16,
                       void* dres_bf16, size_t rows, int C, const float* stat, const float* sums, int relu,
                       void* stream);
+/* One-launch variants for small tensors (rows <= b200_bn_small_rows()): statistics+apply, reduce+apply. */
+size_t b200_bn_small_rows(void);
+int b200_bn_fwd_fused(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C,
+                      const float* gamma, const float* beta, float eps, float momentum, float* stat,
+                      float* running_mean, float* running_var, int relu, void* stream);
+int b200_bn_bwd_fused(const void* dy_bf16, const void* x_bf16, const void* y_bf16, void* dx_bf16, void* dres_bf16,
+                      size_t rows, int C, const float* stat, int relu, float* dgamma, float* dbeta, float beta_accum,
+                      void* stream);
 int b200_maxpool_fwd(const void* x, void* y, uint8_t* argmax, int N, int H, int W, int C, int k, int stride,
                      int pad, void* stream);
 int b200_maxpool_bwd(const void* dy, const uint8_t* argmax, void* dx, int N, int H, int W, int C, int k,

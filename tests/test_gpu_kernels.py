@@ -134,6 +134,31 @@ def test_batchnorm(shape, relu, res):
     assert torch.equal(stat, stat2)
 
 
+@pytest.mark.parametrize("shape,relu,res", [((32, 64, 8, 8), True, True), ((256, 512, 1, 1), True, False), ((16, 128, 4, 4), False, True)])
+def test_batchnorm_fused_small_matches_two_pass(shape, relu, res):
+    """Single-launch BN (small tensors) == the stats/apply and reduce/apply kernels, bit for bit on the statistics."""
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    torch.manual_seed(6)
+    N, C, H, W = shape
+    x = _act(N, C, H, W, dev, 2.0)
+    r = _act(N, C, H, W, dev) if res else None
+    gamma, beta = torch.rand(C, device=dev) + 0.5, torch.randn(C, device=dev)
+    rm1, rv1, rm2, rv2 = torch.zeros(C, device=dev), torch.ones(C, device=dev), torch.zeros(C, device=dev), torch.ones(C, device=dev)
+    stat_a = nv.bn_stats(x, gamma, beta, 1e-5, 0.1, rm1, rv1)
+    y_a = nv.bn_apply(x, r, stat_a, relu)
+    y_b, stat_b = nv.bn_fwd_fused(x, r, gamma, beta, 1e-5, 0.1, rm2, rv2, relu)
+    assert torch.allclose(stat_a, stat_b, rtol=1e-5, atol=1e-6) and torch.equal(y_a, y_b)
+    assert torch.allclose(rm1, rm2, atol=1e-6) and torch.allclose(rv1, rv2, atol=1e-6)
+    dy = _act(N, C, H, W, dev)
+    dg1, db1, dg2, db2 = (torch.zeros(C, device=dev) for _ in range(4))
+    dx_a, dres_a, _ = nv.bn_bwd(dy, x, y_a, stat_a, relu, res, dg1, db1, 0.0)
+    dx_b, dres_b = nv.bn_bwd_fused(dy, x, y_a, stat_a, relu, res, dg2, db2, 0.0)
+    assert _rel_err(dx_b, dx_a) < 1e-3 and _rel_err(dg2, dg1) < 1e-4 and _rel_err(db2, db1) < 1e-4
+    if res:
+        assert torch.equal(dres_a, dres_b)
+
+
 def test_bn_eval():
     from b200ddp.ops import native as nv
     dev = _dev()
