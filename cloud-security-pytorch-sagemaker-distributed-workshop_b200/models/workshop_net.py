@@ -37,4 +37,19 @@ class WorkshopNet(nn.Module):
         return x[:, : self.num_classes] if x.shape[1] != self.num_classes else x
 
 
+    def fused_loss(self, x_nchw_fp32, targets):
+        """Forward + cross-entropy + backward in two kernel launches (CUDA only; `ops.functional`)."""
+        from ..ops import functional as BF
+        return BF.workshop_net_fused_loss(self, x_nchw_fp32, targets)
+
+    def logits_fused(self, x_nchw_fp32):
+        """Inference through the megakernel's forward half (fp32)."""
+        from ..ops import native as nv
+        params = [p.detach() for p in (self.conv1.weight, self.conv1.bias, self.conv2.weight, self.conv2.bias, self.fc1.weight,
+                                       self.fc1.bias, self.fc2.weight, self.fc2.bias, self.fc3.weight, self.fc3.bias)]
+        krsc = not self.conv1.weight.is_contiguous()
+        dummy = torch.zeros(x_nchw_fp32.shape[0], dtype=torch.int64, device=x_nchw_fp32.device)
+        return nv.net_fwd_bwd(x_nchw_fp32.contiguous(), dummy, params, None, krsc, want_logits=True)[1]
+
+
 Net = WorkshopNet   # the reference's class name

@@ -397,3 +397,46 @@ def bce_with_logits(logits, targets):
     if not logits.is_cuda:
         return F.binary_cross_entropy_with_logits(logits.float(), targets.float())
     return _BCEFn.apply(logits, targets)
+
+
+# ------------------------------------------------------------------------------------------------
+# workshop Net: forward + loss + backward as two launches
+# ------------------------------------------------------------------------------------------------
+class _WorkshopNetFusedFn(torch.autograd.Function):
+    """loss = CE(Net(x), targets).  The megakernel produces the gradients during ``forward`` (they land in the
+    flat gradient arena when the parameters carry sinks); ``backward`` only tells the reducer they are ready."""
+
+    @staticmethod
+    def forward(ctx, x, targets, krsc, *params):
+        want = any(ctx.needs_input_grad[3:])
+        sinks = [getattr(p, "_b200_sink", None) for p in params]
+        use_sinks = want and all(s is not None for s in sinks)
+        grads = None
+        if want:
+            grads = [s.flat for s in sinks] if use_sinks else [torch.zeros_like(p) for p in params]
+        loss, _ = nv.net_fwd_bwd(x, targets, [p.detach() for p in params], grads, krsc)
+        ctx.sinks = sinks if use_sinks else None
+        ctx.grads = None if use_sinks else grads
+        return loss
+
+    @staticmethod
+    def backward(ctx, gout):
+        if ctx.sinks is not None:
+            for s_ in ctx.sinks:
+                s_.done()
+            return (None, None, None) + (None,) * len(ctx.sinks)
+        g = ctx.grads
+        if not _unit_loss_grad[0]:
+            g = [t * gout for t in g]
+        return (None, None, None) + tuple(g)
+
+
+def workshop_net_fused_loss(model, x_nchw_fp32, targets):
+    """Mean cross-entropy of the workshop Net on a normalised fp32 NCHW batch, with gradients for every parameter."""
+    params = [model.conv1.weight, model.conv1.bias, model.conv2.weight, model.conv2.bias, model.fc1.weight, model.fc1.bias,
+              model.fc2.weight, model.fc2.bias, model.fc3.weight, model.fc3.bias]
+    w = model.conv1.weight
+    krsc = (not w.is_contiguous()) and w.permute(0, 2, 3, 1).is_contiguous()
+    if not (w.is_contiguous() or krsc) or model.conv2.weight.is_contiguous() == krsc:
+        raise RuntimeError("workshop Net megakernel: unexpected conv weight layout")
+    return _WorkshopNetFusedFn.apply(x_nchw_fp32.contiguous(), targets, bool(krsc), *params)

@@ -352,3 +352,36 @@ def trojan_stamp_(x: torch.Tensor, pattern: torch.Tensor, loc_h: int, loc_w: int
     L.check(L.lib().b200_trojan_stamp(L.ptr(x), c_int(N), c_int(C), c_int(H), c_int(W), L.ptr(pattern), c_int(PC), c_int(ph),
                                       c_int(pw), c_int(loc_h), c_int(loc_w), c_float(alpha), L.ptr(mask), L.stream_ptr()),
             "trojan_stamp")
+
+
+# --------------------------------------------------------------------------------------------
+# workshop Net megakernel
+# --------------------------------------------------------------------------------------------
+_NET_SCRATCH = {}
+
+
+def net_fwd_bwd(x_nchw: torch.Tensor, targets: torch.Tensor, params, grads, krsc: bool, want_logits: bool = False):
+    """Forward + CE loss (+ backward when ``grads`` is a list of 10 fp32 buffers, accumulated into) of the
+    workshop Net.  ``params``: the 10 tensors in state_dict order (storage order per ``krsc``).
+    Returns ``(loss_mean, logits or None)``."""
+    B = x_nchw.shape[0]
+    assert x_nchw.dtype == torch.float32 and x_nchw.is_contiguous() and tuple(x_nchw.shape[1:]) == (3, 32, 32)
+    dev = x_nchw.device
+    lib = L.lib()
+    lib.b200_net_scratch_bytes.restype = c_size_t
+    need = lib.b200_net_scratch_bytes(c_int(B))
+    key = (dev.index, B)
+    sc = _NET_SCRATCH.get(key)
+    if sc is None:
+        sc = torch.zeros(need, dtype=torch.uint8, device=dev)
+        _NET_SCRATCH[key] = sc
+    row_loss = torch.empty(B, dtype=torch.float32, device=dev)
+    loss = torch.empty((), dtype=torch.float32, device=dev)
+    logits = torch.empty((B, 10), dtype=torch.float32, device=dev) if want_logits else None
+    P = (c_void_p * 10)(*[t.data_ptr() for t in params])
+    G = (c_void_p * 10)(*[t.data_ptr() for t in grads]) if grads is not None else None
+    L.check(lib.b200_net_fwd_bwd(L.ptr(x_nchw), L.ptr(targets), c_int(B), P, G, c_int(int(krsc)), L.ptr(row_loss), L.ptr(loss),
+                                 L.ptr(logits), L.ptr(sc), c_size_t(sc.numel()), L.stream_ptr()), "net_fwd_bwd")
+    if grads is not None:
+        L.LAUNCHES[0] += 1          # two kernels per call
+    return loss, logits

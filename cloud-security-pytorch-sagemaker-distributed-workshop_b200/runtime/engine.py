@@ -37,6 +37,11 @@ class TrainStep:
         self.steps_done = 0
         self._graph = None
         self._captured_batch = None
+        import os
+        from ..models.workshop_net import WorkshopNet
+        core = model.module if hasattr(model, "module") else model
+        self._net_mega = core if (isinstance(core, WorkshopNet) and self.cuda and self.image_shape == (32, 32, 3)
+                                  and os.environ.get("B200DDP_NET_MEGAKERNEL", "1") != "0") else None
         self.mean_t = torch.tensor(mean, dtype=torch.float32, device=self.device)
         self.inv_std_t = 1.0 / torch.tensor(std, dtype=torch.float32, device=self.device)
         self._mean, self._std = mean, std
@@ -59,6 +64,14 @@ class TrainStep:
 
     def _body(self, x_u8, y, offsets):
         from ..ops import native as nv
+        if self.cuda and self._net_mega is not None:
+            # workshop Net: augmentation kernel + forward/loss/backward megakernel (2 launches) + fused SGD
+            inp = nv.augment(x_u8, offsets if self.augment else None, self.mean_t, self.inv_std_t, nchw_fp32=True)
+            self.optimizer.zero_grad()
+            loss = self._net_mega.fused_loss(inp, y)
+            loss.backward()
+            self.optimizer.step()
+            return loss.detach()
         if self.cuda:
             cin = 8
             inp = nv.augment(x_u8, offsets if self.augment else None, self.mean_t, self.inv_std_t, c_out=cin)

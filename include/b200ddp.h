@@ -183,6 +183,17 @@ int b200_trojan_stamp(float* x, int N, int C, int H, int W, const float* pattern
                       int p_h, int p_w, int loc_h, int loc_w, float alpha, const uint8_t* mask, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
+ * Workshop `Net` megakernel (…native-cpu.py:22-39,146-156): forward + softmax-CE + backward of the LeNet-style
+ * CIFAR-10 CNN in two launches, fp32.  params/grads: 10 pointers in state_dict order; grads (may be NULL) are
+ * ACCUMULATED (flat arena semantics); krsc != 0: conv weights/grads are channels-last [co][r][s][ci].
+ * scratch: b200_net_scratch_bytes(batch) bytes, zero before first use (fc1 operands + a ticket counter).
+ * ------------------------------------------------------------------------------------------- */
+size_t b200_net_scratch_bytes(int batch);
+int b200_net_fwd_bwd(const float* x_nchw, const int64_t* targets, int batch, const float* const* params,
+                     float* const* grads, int krsc, float* row_loss, float* loss_mean, float* logits,
+                     void* scratch, size_t scratch_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
  * Tensor-core layers: implicit-GEMM convolution and linear (a 1x1 convolution on [M,1,1,K]) on
  * tcgen05 + TMEM (replace cuDNN conv fwd/dgrad/wgrad and cuBLAS GEMM under nn.Conv2d / nn.Linear —
  * torchvision resnet18 via …smddp-gpu.py:32; model_lib/cifar10_cnn_model.py:11-18).

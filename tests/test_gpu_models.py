@@ -177,3 +177,37 @@ def test_colsum_bias_grad():
     ref = 1.0 + dy.float().sum(0)
     assert torch.allclose(out[:84], ref[:84], atol=1e-2, rtol=1e-3)
     assert bool((out[84:] == 1.0).all())
+
+
+@pytest.mark.parametrize("wrapped", [False, True])
+def test_workshop_net_megakernel_matches_cpu_fp32(wrapped, pg):
+    """W15: two-launch fp32 forward+loss+backward of the workshop Net == plain PyTorch fp32 autograd on the CPU."""
+    from b200ddp.models import get_model
+    from b200ddp.ops import functional as BF
+    dev = _dev()
+    torch.manual_seed(11)
+    ref = get_model("custom")
+    net = copy.deepcopy(ref).to(dev)
+    x = torch.randn(37, 3, 32, 32)
+    y = torch.randint(0, 10, (37,))
+    loss_r = F.cross_entropy(ref(x), y)
+    loss_r.backward()
+    BF.assume_unit_loss_grad(False)
+    if wrapped:                      # DDP: channels-last conv weights, gradients land in the flat arena
+        ddp = pg.DistributedDataParallel(net)
+        ddp.zero_grad()
+    loss = net.fused_loss(x.to(dev), y.to(dev))
+    loss.backward()
+    torch.cuda.synchronize()
+    assert abs(float(loss.detach()) - float(loss_r.detach())) < 1e-4
+    for (n, a), (_, b) in zip(ref.named_parameters(), net.named_parameters()):
+        assert b.grad is not None, n
+        assert _rel(b.grad, a.grad) < 2e-4, (n, _rel(b.grad, a.grad))
+    with torch.no_grad():
+        assert torch.allclose(net.logits_fused(x.to(dev)).cpu(), ref(x), atol=1e-4)
+    # twice in a row: the ticket counter reset itself, gradients accumulate like autograd's
+    loss2 = net.fused_loss(x.to(dev), y.to(dev))
+    loss2.backward()
+    torch.cuda.synchronize()
+    assert abs(float(loss2.detach()) - float(loss_r.detach())) < 1e-4
+    assert _rel(net.fc1.weight.grad, 2 * ref.fc1.weight.grad) < 2e-4
