@@ -37,10 +37,11 @@ class WorkshopNet(nn.Module):
         return x[:, : self.num_classes] if x.shape[1] != self.num_classes else x
 
 
-    def fused_loss(self, x_nchw_fp32, targets):
-        """Forward + cross-entropy + backward in two kernel launches (CUDA only; `ops.functional`)."""
+    def fused_loss(self, x, targets, aug=None):
+        """Forward + cross-entropy + backward in two kernel launches (CUDA only; `ops.functional`).  ``x`` is the
+        normalised fp32 NCHW batch, or the raw uint8 NHWC batch with ``aug = (offsets | None, mean, inv_std)``."""
         from ..ops import functional as BF
-        return BF.workshop_net_fused_loss(self, x_nchw_fp32, targets)
+        return BF.workshop_net_fused_loss(self, x, targets, aug)
 
     def logits_fused(self, x_nchw_fp32):
         """Inference through the megakernel's forward half (fp32)."""

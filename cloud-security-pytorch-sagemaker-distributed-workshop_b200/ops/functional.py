@@ -407,14 +407,16 @@ class _WorkshopNetFusedFn(torch.autograd.Function):
     flat gradient arena when the parameters carry sinks); ``backward`` only tells the reducer they are ready."""
 
     @staticmethod
-    def forward(ctx, x, targets, krsc, *params):
-        want = any(ctx.needs_input_grad[3:])
+    def forward(ctx, x, targets, krsc, aug, loss_out, *params):
+        want = any(ctx.needs_input_grad[5:])
         sinks = [getattr(p, "_b200_sink", None) for p in params]
         use_sinks = want and all(s is not None for s in sinks)
         grads = None
         if want:
             grads = [s.flat for s in sinks] if use_sinks else [torch.zeros_like(p) for p in params]
-        loss, _ = nv.net_fwd_bwd(x, targets, [p.detach() for p in params], grads, krsc)
+        loss, _ = nv.net_fwd_bwd(x, targets, [p.detach() for p in params], grads, krsc, aug=aug, loss_out=loss_out)
+        if loss_out is not None:
+            ctx.mark_dirty(loss_out)
         ctx.sinks = sinks if use_sinks else None
         ctx.grads = None if use_sinks else grads
         return loss
@@ -424,19 +426,20 @@ class _WorkshopNetFusedFn(torch.autograd.Function):
         if ctx.sinks is not None:
             for s_ in ctx.sinks:
                 s_.done()
-            return (None, None, None) + (None,) * len(ctx.sinks)
+            return (None,) * (5 + len(ctx.sinks))
         g = ctx.grads
         if not _unit_loss_grad[0]:
             g = [t * gout for t in g]
-        return (None, None, None) + tuple(g)
+        return (None,) * 5 + tuple(g)
 
 
-def workshop_net_fused_loss(model, x_nchw_fp32, targets):
-    """Mean cross-entropy of the workshop Net on a normalised fp32 NCHW batch, with gradients for every parameter."""
+def workshop_net_fused_loss(model, x, targets, aug=None):
+    """Mean cross-entropy of the workshop Net with gradients for every parameter.  ``x``: a normalised fp32 NCHW batch, or
+    the raw uint8 NHWC batch with ``aug = (offsets or None, mean, inv_std)`` (augmentation fused into the kernel)."""
     params = [model.conv1.weight, model.conv1.bias, model.conv2.weight, model.conv2.bias, model.fc1.weight, model.fc1.bias,
               model.fc2.weight, model.fc2.bias, model.fc3.weight, model.fc3.bias]
     w = model.conv1.weight
     krsc = (not w.is_contiguous()) and w.permute(0, 2, 3, 1).is_contiguous()
     if not (w.is_contiguous() or krsc) or model.conv2.weight.is_contiguous() == krsc:
         raise RuntimeError("workshop Net megakernel: unexpected conv weight layout")
-    return _WorkshopNetFusedFn.apply(x_nchw_fp32.contiguous(), targets, bool(krsc), *params)
+    return _WorkshopNetFusedFn.apply(x.contiguous(), targets, bool(krsc), aug, None, *params)

@@ -360,13 +360,14 @@ def trojan_stamp_(x: torch.Tensor, pattern: torch.Tensor, loc_h: int, loc_w: int
 _NET_SCRATCH = {}
 
 
-def net_fwd_bwd(x_nchw: torch.Tensor, targets: torch.Tensor, params, grads, krsc: bool, want_logits: bool = False):
+def net_fwd_bwd(x: torch.Tensor, targets: torch.Tensor, params, grads, krsc: bool, want_logits: bool = False,
+                aug=None, loss_out: Optional[torch.Tensor] = None):
     """Forward + CE loss (+ backward when ``grads`` is a list of 10 fp32 buffers, accumulated into) of the
-    workshop Net.  ``params``: the 10 tensors in state_dict order (storage order per ``krsc``).
-    Returns ``(loss_mean, logits or None)``."""
-    B = x_nchw.shape[0]
-    assert x_nchw.dtype == torch.float32 and x_nchw.is_contiguous() and tuple(x_nchw.shape[1:]) == (3, 32, 32)
-    dev = x_nchw.device
+    workshop Net.  ``x``: normalised fp32 NCHW batch, or the raw uint8 NHWC batch with ``aug = (offsets or None,
+    mean, inv_std)`` -- crop / flip / normalise then happen inside the kernel.  ``params``: the 10 tensors in
+    state_dict order (storage order per ``krsc``).  Returns ``(loss_mean, logits or None)``."""
+    B = x.shape[0]
+    dev = x.device
     lib = L.lib()
     lib.b200_net_scratch_bytes.restype = c_size_t
     need = lib.b200_net_scratch_bytes(c_int(B))
@@ -376,12 +377,20 @@ def net_fwd_bwd(x_nchw: torch.Tensor, targets: torch.Tensor, params, grads, krsc
         sc = torch.zeros(need, dtype=torch.uint8, device=dev)
         _NET_SCRATCH[key] = sc
     row_loss = torch.empty(B, dtype=torch.float32, device=dev)
-    loss = torch.empty((), dtype=torch.float32, device=dev)
+    loss = loss_out if loss_out is not None else torch.empty((), dtype=torch.float32, device=dev)
     logits = torch.empty((B, 10), dtype=torch.float32, device=dev) if want_logits else None
     P = (c_void_p * 10)(*[t.data_ptr() for t in params])
     G = (c_void_p * 10)(*[t.data_ptr() for t in grads]) if grads is not None else None
-    L.check(lib.b200_net_fwd_bwd(L.ptr(x_nchw), L.ptr(targets), c_int(B), P, G, c_int(int(krsc)), L.ptr(row_loss), L.ptr(loss),
-                                 L.ptr(logits), L.ptr(sc), c_size_t(sc.numel()), L.stream_ptr()), "net_fwd_bwd")
+    if x.dtype == torch.uint8:
+        assert aug is not None and x.is_contiguous() and tuple(x.shape[1:]) == (32, 32, 3)
+        offsets, mean, inv_std = aug
+        L.check(lib.b200_net_fwd_bwd_u8(L.ptr(x), L.ptr(offsets), L.ptr(mean), L.ptr(inv_std), L.ptr(targets), c_int(B), P, G,
+                                        c_int(int(krsc)), L.ptr(row_loss), L.ptr(loss), L.ptr(logits), L.ptr(sc),
+                                        c_size_t(sc.numel()), L.stream_ptr()), "net_fwd_bwd_u8")
+    else:
+        assert x.dtype == torch.float32 and x.is_contiguous() and tuple(x.shape[1:]) == (3, 32, 32)
+        L.check(lib.b200_net_fwd_bwd(L.ptr(x), L.ptr(targets), c_int(B), P, G, c_int(int(krsc)), L.ptr(row_loss), L.ptr(loss),
+                                     L.ptr(logits), L.ptr(sc), c_size_t(sc.numel()), L.stream_ptr()), "net_fwd_bwd")
     if grads is not None:
         L.LAUNCHES[0] += 1          # two kernels per call
     return loss, logits

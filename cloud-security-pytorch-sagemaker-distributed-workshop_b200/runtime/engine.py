@@ -52,6 +52,7 @@ class TrainStep:
             self.static_y = torch.zeros((B,), dtype=torch.int64, device=self.device)
             self.static_off = torch.zeros((B, 3), dtype=torch.int32, device=self.device)
             self.static_loss = torch.zeros((), dtype=torch.float32, device=self.device)
+            self._one = torch.ones((), dtype=torch.float32, device=self.device)   # dL/dL, so backward() launches no fill
             self.pin_off = torch.zeros((B, 3), dtype=torch.int32).pin_memory()
             self.pin_loss = torch.zeros((), dtype=torch.float32).pin_memory()
             BF.assume_unit_loss_grad(True)
@@ -65,11 +66,10 @@ class TrainStep:
     def _body(self, x_u8, y, offsets):
         from ..ops import native as nv
         if self.cuda and self._net_mega is not None:
-            # workshop Net: augmentation kernel + forward/loss/backward megakernel (2 launches) + fused SGD
-            inp = nv.augment(x_u8, offsets if self.augment else None, self.mean_t, self.inv_std_t, nchw_fp32=True)
+            # workshop Net: augmentation + forward/loss/backward megakernel (2 launches) + fused SGD
             self.optimizer.zero_grad()
-            loss = self._net_mega.fused_loss(inp, y)
-            loss.backward()
+            loss = self._net_mega.fused_loss(x_u8, y, aug=(offsets if self.augment else None, self.mean_t, self.inv_std_t))
+            loss.backward(self._one)
             self.optimizer.step()
             return loss.detach()
         if self.cuda:
@@ -80,7 +80,7 @@ class TrainStep:
         self.optimizer.zero_grad()
         out = self.model(inp)
         loss = self.criterion(out, y)
-        loss.backward()
+        loss.backward(self._one if self.cuda else None)
         self.optimizer.step()
         # detach: a live loss keeps last step's autograd graph (and its AccumulateGrad nodes, which are
         # bound to the stream they were created on) alive, which breaks CUDA-graph capture

@@ -189,9 +189,17 @@ int b200_trojan_stamp(float* x, int N, int C, int H, int W, const float* pattern
  * scratch: b200_net_scratch_bytes(batch) bytes, zero before first use (fc1 operands + a ticket counter).
  * ------------------------------------------------------------------------------------------- */
 size_t b200_net_scratch_bytes(int batch);
+/* debug: 32 clock64 stamps of CTA 0's phases go to `buf` (device memory; NULL stops) */
+void b200_net_set_profile_buffer(long long* buf);
 int b200_net_fwd_bwd(const float* x_nchw, const int64_t* targets, int batch, const float* const* params,
                      float* const* grads, int krsc, float* row_loss, float* loss_mean, float* logits,
                      void* scratch, size_t scratch_bytes, void* stream);
+/* same, from the raw uint8 NHWC batch: RandomCrop(32,4)+flip (offsets [B][3] = dy, dx, flip; NULL = none) and
+   Normalize(mean, 1/std) are applied while the image is staged into shared memory */
+int b200_net_fwd_bwd_u8(const uint8_t* img_nhwc, const int32_t* offsets, const float* mean, const float* inv_std,
+                        const int64_t* targets, int batch, const float* const* params, float* const* grads, int krsc,
+                        float* row_loss, float* loss_mean, float* logits, void* scratch, size_t scratch_bytes,
+                        void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Tensor-core layers: implicit-GEMM convolution and linear (a 1x1 convolution on [M,1,1,K]) on

@@ -36,3 +36,26 @@ res["fwd_only_us"] = op_time(lambda: nv.net_fwd_bwd(x, y, params, None, False))
 res["fwd_bwd_us"] = op_time(lambda: nv.net_fwd_bwd(x, y, params, grads, False))
 res["augment_us"] = op_time(lambda: nv.augment(xu, None, mean, inv, nchw_fp32=True))
 print(json.dumps(res, indent=1))
+
+# ---- phase timeline of CTA 0 (clock64 stamps; first image) -- warm, plain launches
+import ctypes
+from b200ddp.ops import _lib as L
+prof = torch.zeros(32, dtype=torch.int64, device=dev)
+L.lib().b200_net_set_profile_buffer(ctypes.c_void_p(prof.data_ptr()))
+for _ in range(3):
+    nv.net_fwd_bwd(x, y, params, grads, False)
+torch.cuda.synchronize()
+L.lib().b200_net_set_profile_buffer(ctypes.c_void_p(0))
+st = prof.cpu().tolist()
+names = ["setup (weights->smem)", "load image", "conv1+pool", "conv2+pool", "fc1", "fc2+fc3+loss", "dh2+dh1", "dp2 stream",
+         "dp2 sum+g2", "conv2 dgrad || conv2 wgrad+bias+scratch", "g1", "conv1 wgrad", None, "flush (red.add)", "ticket+loss"]
+order = list(range(16))
+tl = {}
+for k in range(len(order) - 1):
+    a, b = st[order[k]], st[order[k + 1]]
+    if names[k] is None:
+        tl["(remaining images of CTA 0)"] = b - a
+    else:
+        tl[names[k]] = b - a
+tl["total_cycles"] = st[15] - st[0]
+print(json.dumps({"phase_cycles_cta0": tl}, indent=1))

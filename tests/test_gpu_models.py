@@ -211,3 +211,37 @@ def test_workshop_net_megakernel_matches_cpu_fp32(wrapped, pg):
     torch.cuda.synchronize()
     assert abs(float(loss2.detach()) - float(loss_r.detach())) < 1e-4
     assert _rel(net.fc1.weight.grad, 2 * ref.fc1.weight.grad) < 2e-4
+
+
+def test_workshop_net_megakernel_uint8_input_equals_augment_then_fp32_path(pg):
+    """The megakernel's fused crop/flip/normalise of a raw uint8 batch == b200_augment followed by the fp32 entry point,
+    with a batch large enough that CTAs loop over several images (double-buffered prefetch)."""
+    from b200ddp.models import get_model
+    from b200ddp.ops import functional as BF, native as nv
+    dev = _dev()
+    torch.manual_seed(5)
+    net = get_model("custom").to(dev)
+    B = 333
+    xu = torch.randint(0, 256, (B, 32, 32, 3), dtype=torch.uint8, device=dev)
+    y = torch.randint(0, 10, (B,), device=dev)
+    off = torch.stack([torch.randint(0, 9, (B,)), torch.randint(0, 9, (B,)), torch.randint(0, 2, (B,))], 1).to(torch.int32).to(dev)
+    mean = torch.tensor((0.4914, 0.4822, 0.4465), device=dev)
+    inv = 1.0 / torch.tensor((0.2023, 0.1994, 0.2010), device=dev)
+    BF.assume_unit_loss_grad(False)
+    grads = {}
+    for name, offsets in (("plain", None), ("aug", off)):
+        for mode in ("fp32", "u8"):
+            net.zero_grad()
+            if mode == "fp32":
+                loss = net.fused_loss(nv.augment(xu, offsets, mean, inv, nchw_fp32=True), y)
+            else:
+                loss = net.fused_loss(xu, y, aug=(offsets, mean, inv))
+            loss.backward()
+            torch.cuda.synchronize()
+            grads[(name, mode)] = (float(loss.detach()), [p.grad.clone() for p in net.parameters()])
+        la, ga = grads[(name, "fp32")]
+        lb, gb = grads[(name, "u8")]
+        assert abs(la - lb) < 1e-6, (name, la, lb)
+        for a, b in zip(ga, gb):
+            assert _rel(a, b) < 1e-5, name           # same arithmetic; only the order of the red.adds may differ
+    assert abs(grads[("plain", "u8")][0] - grads[("aug", "u8")][0]) > 0      # the offsets do something
