@@ -48,15 +48,27 @@ class TrainStep:
         if self.cuda:
             H, W, C = self.image_shape
             B = self.batch_size
-            self.static_x = torch.zeros((B, H, W, C), dtype=torch.uint8, device=self.device)
-            self.static_y = torch.zeros((B,), dtype=torch.int64, device=self.device)
-            self.static_off = torch.zeros((B, 3), dtype=torch.int32, device=self.device)
+            # the graph's static inputs are views of ONE blob (pixels | labels | crop offsets), so the pipelined path
+            # moves a staged batch into place with a single device copy
+            self._nx = (B * H * W * C + 255) // 256 * 256
+            self._ny = (B * 8 + 255) // 256 * 256
+            self._nblob = self._nx + self._ny + B * 12
+            self.static_blob = torch.zeros(self._nblob, dtype=torch.uint8, device=self.device)
+            self.static_x, self.static_y, self.static_off = self._views(self.static_blob)
             self.static_loss = torch.zeros((), dtype=torch.float32, device=self.device)
             self._one = torch.ones((), dtype=torch.float32, device=self.device)   # dL/dL, so backward() launches no fill
             self.pin_off = torch.zeros((B, 3), dtype=torch.int32).pin_memory()
             self.pin_loss = torch.zeros((), dtype=torch.float32).pin_memory()
             BF.assume_unit_loss_grad(True)
             bmod.defer_bn_counters(True)
+
+    def _views(self, blob: torch.Tensor):
+        H, W, C = self.image_shape
+        B = self.batch_size
+        x = blob[:B * H * W * C].view(B, H, W, C)
+        y = blob[self._nx:self._nx + B * 8].view(torch.int64)
+        off = blob[self._nx + self._ny:self._nx + self._ny + B * 12].view(torch.int32).view(B, 3)
+        return x, y, off
 
     # ------------------------------------------------------------------ one step, eager
     def _draw_offsets(self, n: int) -> torch.Tensor:
@@ -138,6 +150,73 @@ class TrainStep:
         loss = self._body(xd, yd, od)
         self.steps_done += 1
         return float(loss.item()) if need_loss else None
+
+    def pipeline(self, batches, need_loss: bool = True):
+        """Run one optimisation step per ``(x_u8, y)`` host batch (pinned memory) and yield one loss per step.
+
+        Software pipeline of depth 2: batch k+1 is uploaded on a copy stream into a staging blob while step k
+        computes, one device copy moves it into the graph's static inputs, and the loss of step k is read back
+        asynchronously and yielded while step k+1 runs (so the caller sees each loss one step late; every loss is
+        still read, in order).  Falls back to plain ``__call__`` without a GPU / graph or for a short batch."""
+        if not (self.cuda and self.use_graph):
+            for x, y in batches:
+                yield self(x, y, need_loss=need_loss)
+            return
+        dev = self.device
+        if not hasattr(self, "_pipe"):
+            cs = torch.cuda.Stream(device=dev)
+            self._pipe = {
+                "cs": cs,
+                "stage": [torch.zeros_like(self.static_blob) for _ in range(2)],
+                "pin_off": [torch.zeros((self.batch_size, 3), dtype=torch.int32).pin_memory() for _ in range(2)],
+                "pin_loss": [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)],
+                "h2d": [torch.cuda.Event() for _ in range(2)],
+                "free": [torch.cuda.Event() for _ in range(2)],
+                "ready": [torch.cuda.Event() for _ in range(2)],
+            }
+            self._pipe["views"] = [self._views(b) for b in self._pipe["stage"]]
+        P = self._pipe
+        cur = torch.cuda.current_stream(dev)
+        pending = None                       # slot whose loss has not been yielded yet
+        k = 0
+        for x, y in batches:
+            if x.shape[0] != self.batch_size or self._graph is None:
+                if pending is not None:
+                    P["ready"][pending].synchronize()
+                    yield float(P["pin_loss"][pending].item()) if need_loss else None
+                    pending = None
+                yield self(x, y, need_loss=need_loss)
+                continue
+            slot = k & 1
+            sx, sy, so = P["views"][slot]
+            if k >= 2:
+                P["h2d"][slot].synchronize()             # pinned offsets of step k-2 have been consumed
+                P["cs"].wait_event(P["free"][slot])      # ... and its staged batch has been moved into place
+            else:
+                P["cs"].wait_stream(cur)
+            with torch.cuda.stream(P["cs"]):
+                sx.copy_(x, non_blocking=True)
+                sy.copy_(y, non_blocking=True)
+                if self.augment:
+                    P["pin_off"][slot].copy_(self._draw_offsets(self.batch_size))
+                    so.copy_(P["pin_off"][slot], non_blocking=True)
+                P["h2d"][slot].record(P["cs"])
+            cur.wait_event(P["h2d"][slot])
+            self.static_blob.copy_(P["stage"][slot], non_blocking=True)
+            P["free"][slot].record(cur)
+            self._graph.replay()
+            self.steps_done += 1
+            if need_loss:
+                P["pin_loss"][slot].copy_(self.static_loss, non_blocking=True)
+            P["ready"][slot].record(cur)
+            if pending is not None:
+                P["ready"][pending].synchronize()
+                yield float(P["pin_loss"][pending].item()) if need_loss else None
+            pending = slot
+            k += 1
+        if pending is not None:
+            P["ready"][pending].synchronize()
+            yield float(P["pin_loss"][pending].item()) if need_loss else None
 
     def flush_counters(self):
         if self.cuda:

@@ -245,3 +245,31 @@ def test_workshop_net_megakernel_uint8_input_equals_augment_then_fp32_path(pg):
         for a, b in zip(ga, gb):
             assert _rel(a, b) < 1e-5, name           # same arithmetic; only the order of the red.adds may differ
     assert abs(grads[("plain", "u8")][0] - grads[("aug", "u8")][0]) > 0      # the offsets do something
+
+
+def test_pipelined_steps_equal_sequential_steps(pg):
+    """TrainStep.pipeline (upload of batch k+1 overlapped with step k, losses read one step late) computes exactly what
+    calling the step once per batch computes: same losses in the same order, same final weights."""
+    from b200ddp.models import get_model
+    from b200ddp.nn import CrossEntropyLoss
+    from b200ddp.ops import optim as boptim
+    from b200ddp.runtime.engine import TrainStep
+    dev = _dev()
+    xs = torch.randint(0, 256, (7, 64, 32, 32, 3), dtype=torch.uint8).pin_memory()
+    ys = torch.randint(0, 10, (7, 64)).pin_memory()
+    results = {}
+    for mode in ("sequential", "pipeline"):
+        torch.manual_seed(9)
+        net = pg.DistributedDataParallel(get_model("custom").to(dev))
+        opt = boptim.SGD(net.parameters(), lr=0.05, momentum=0.9)
+        step = TrainStep(net, CrossEntropyLoss(), opt, 64, device=dev, graph=True, seed=2, augment=True, warmup_iters=3)
+        step(xs[0], ys[0])                       # capture (3 warm-up steps on batch 0) + one step
+        if mode == "sequential":
+            losses = [step(xs[i], ys[i], need_loss=True) for i in range(1, 7)]
+        else:
+            losses = list(step.pipeline((xs[i], ys[i]) for i in range(1, 7)))
+        torch.cuda.synchronize()
+        results[mode] = (losses, net.flat_params.clone())
+    a, b = results["sequential"], results["pipeline"]
+    assert len(b[0]) == 6 and all(abs(u - v) < 1e-5 for u, v in zip(a[0], b[0])), (a[0], b[0])
+    assert _rel(b[1], a[1]) < 1e-5
