@@ -158,6 +158,15 @@ class AudioModel(_Base):
 
     def forward(self, x):
         x = self._in(x)
+        if x.is_cuda:
+            # native path: FFT + mel + dB in one kernel, LSTM recurrence with W_hh in registers.
+            # A waveform that needs its own gradient (meta-classifier query tuning) goes through the torch.stft features.
+            from ...ops import native as nv
+            feats = self.features(x) if x.requires_grad else nv.mel_frontend(x.float().contiguous(), self._window, self._mel)
+            lstm_out = BF.lstm(feats, self.lstm)
+            att = BF.linear_f32(lstm_out, self.lstm_att.weight, self.lstm_att.bias).squeeze(2)
+            emb = (lstm_out * F.softmax(att, dim=1).unsqueeze(2)).sum(1)
+            return BF.linear_f32(emb, self.output.weight, self.output.bias)
         lstm_out, _ = self.lstm(self.features(x))
         att_val = F.softmax(self.lstm_att(lstm_out).squeeze(2), dim=1)
         emb = (lstm_out * att_val.unsqueeze(2)).sum(1)
@@ -209,10 +218,27 @@ class RTNLPModel(_Base):
         return F.max_pool1d(x, x.size(2)).squeeze(2)
 
     def forward(self, x):
-        return self.emb_forward(self.embed_static.calc_emb(self._in(x)).unsqueeze(1))
+        x = self._in(x)
+        table = self.embed_static.embed.weight
+        if x.is_cuda and table.is_cuda:
+            from ...ops import native as nv
+            B, Ls = x.shape
+            return self._native_head(nv.gather_rows(table, x.long(), pad_rows=4), B, Ls)      # embedding gather kernel (W20)
+        return self.emb_forward(self.embed_static.calc_emb(x).unsqueeze(1))
+
+    def _native_head(self, e_flat, B, Ls):
+        """e_flat [B*Ls + 4, 300] (4 zero rows of padding): three (k x 300) convs as GEMMs over overlapping rows +
+        fused bias/ReLU/max-over-time, dropout, fp32 linear."""
+        x = torch.cat([BF.text_conv_pool(e_flat, B, Ls, c) for c in (self.conv1_3, self.conv1_4, self.conv1_5)], dim=1)
+        x = F.dropout(x, 0.5, training=self.training)
+        return BF.linear_f32(x, self.output.weight, self.output.bias).squeeze(1)
 
     def emb_forward(self, x):
         x = self._in(x)
+        if x.is_cuda:
+            B, _, Ls, D = x.shape
+            e_flat = torch.cat([x.float().reshape(B * Ls, D), x.new_zeros((4, D), dtype=torch.float32)], 0)
+            return self._native_head(e_flat, B, Ls)
         x = torch.cat([self.conv_and_pool(x, c) for c in (self.conv1_3, self.conv1_4, self.conv1_5)], dim=1)
         x = F.dropout(x, 0.5, training=self.training)
         return self.output(x).squeeze(1)

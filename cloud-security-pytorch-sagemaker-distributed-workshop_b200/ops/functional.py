@@ -443,3 +443,112 @@ def workshop_net_fused_loss(model, x, targets, aug=None):
     if not (w.is_contiguous() or krsc) or model.conv2.weight.is_contiguous() == krsc:
         raise RuntimeError("workshop Net megakernel: unexpected conv weight layout")
     return _WorkshopNetFusedFn.apply(x.contiguous(), targets, bool(krsc), aug, None, *params)
+
+
+# ------------------------------------------------------------------------------------------------
+# fp32 sequence-model pieces of the MNTD zoo (csrc/seq.cu)
+# ------------------------------------------------------------------------------------------------
+class _LinearF32Fn(torch.autograd.Function):
+    """y = x W^T + b in fp32 on the CUDA cores (strided sgemm) -- the heads of the audio / text models."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        x2 = x.reshape(-1, x.shape[-1])
+        y = nv.sgemm(x2, w.t(), bias=b)
+        ctx.save_for_backward(x2, w)
+        ctx.has_bias = b is not None
+        ctx.xshape = x.shape
+        return y.view(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1]).contiguous()
+        dx = nv.sgemm(dy2, w).view(ctx.xshape) if ctx.needs_input_grad[0] else None
+        dw = nv.sgemm(dy2.t(), x2) if ctx.needs_input_grad[1] else None
+        db = None
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = nv.sgemm(torch.ones((1, dy2.shape[0]), dtype=torch.float32, device=dy2.device), dy2).view(-1)
+        return dx, dw, db
+
+
+def linear_f32(x, w, b=None):
+    if not x.is_cuda:
+        return F.linear(x, w, b)
+    return _LinearF32Fn.apply(x.float(), w, b)
+
+
+class _LSTMLayerFn(torch.autograd.Function):
+    """One ``nn.LSTM`` layer (batch_first, zero initial state): input projection as one GEMM over [B*T], the recurrence in
+    ``lstm_rec_fwd`` (W_hh rows in registers), BPTT in ``lstm_rec_bwd`` followed by three GEMMs for dW_ih, dW_hh, dx."""
+
+    @staticmethod
+    def forward(ctx, x, w_ih, w_hh, b_ih, b_hh):
+        B, T, I = x.shape
+        x2 = x.reshape(B * T, I)
+        pre = nv.sgemm(x2, w_ih.t(), bias=(b_ih + b_hh))
+        hseq, gates, cseq = nv.lstm_rec_fwd(pre.view(B, T, -1), w_hh.contiguous())
+        ctx.save_for_backward(x2, w_ih, w_hh, hseq, gates, cseq)
+        return hseq
+
+    @staticmethod
+    def backward(ctx, dh):
+        x2, w_ih, w_hh, hseq, gates, cseq = ctx.saved_tensors
+        B, T, H = hseq.shape
+        dg = nv.lstm_rec_bwd(dh.contiguous(), gates, cseq, w_hh.contiguous()).view(B * T, 4 * H)
+        hprev = torch.cat([torch.zeros((B, 1, H), dtype=hseq.dtype, device=hseq.device), hseq[:, :-1]], 1).reshape(B * T, H)
+        dw_hh = nv.sgemm(dg.t(), hprev)
+        dw_ih = nv.sgemm(dg.t(), x2)
+        db = nv.sgemm(torch.ones((1, B * T), dtype=torch.float32, device=dg.device), dg).view(-1)
+        dx = nv.sgemm(dg, w_ih).view(B, T, -1) if ctx.needs_input_grad[0] else None
+        return dx, dw_ih, dw_hh, db, db
+
+
+def lstm(x, module: torch.nn.LSTM):
+    """``nn.LSTM`` forward (all layers, batch_first, zero initial state, no dropout) on this package's kernels."""
+    assert module.batch_first and not module.bidirectional and module.proj_size == 0
+    h = x.float()
+    for layer in range(module.num_layers):
+        p = [getattr(module, "%s_l%d" % (n, layer)) for n in ("weight_ih", "weight_hh", "bias_ih", "bias_hh")]
+        h = _LSTMLayerFn.apply(h, *p)
+    return h
+
+
+class _TextConvPoolFn(torch.autograd.Function):
+    """max_t relu(conv_{k x D}(E) + b) for a [B, L, D] embedding block, conv as a GEMM over overlapping rows of E
+    (row (b, t) of the im2col matrix is the k*D floats starting at E[b, t]: no copy), then fused bias+ReLU+max-over-time."""
+
+    @staticmethod
+    def forward(ctx, e_flat, B, Ls, w, bias):
+        # e_flat: [B*Ls + pad, D] contiguous with >= k-1 zero pad rows so that every window read stays in bounds
+        N, k, D = w.shape[0], w.shape[2], w.shape[3]
+        assert e_flat.shape[0] >= B * Ls + k - 1 and e_flat.is_contiguous()
+        w2 = w.reshape(N, k * D)
+        A = e_flat.as_strided((B * Ls, k * D), (D, 1))
+        C = nv.sgemm(A, w2.t())
+        feat = torch.empty((B, N), dtype=torch.float32, device=e_flat.device)
+        arg = nv.textcnn_pool_fwd(C, bias, feat, 0, B, Ls, k)
+        ctx.save_for_backward(e_flat, w2, feat, arg)
+        ctx.dims = (B, Ls, N, k, D)
+        return feat
+
+    @staticmethod
+    def backward(ctx, dfeat):
+        e_flat, w2, feat, arg = ctx.saved_tensors
+        B, Ls, N, k, D = ctx.dims
+        dC = nv.textcnn_pool_bwd(dfeat.contiguous(), feat, arg, 0, B, Ls)
+        A = e_flat.as_strided((B * Ls, k * D), (D, 1))
+        dw = nv.sgemm(dC.t(), A).view(N, 1, k, D)
+        db = nv.sgemm(torch.ones((1, B * Ls), dtype=torch.float32, device=dC.device), dC).view(-1)
+        de = None
+        if ctx.needs_input_grad[0]:
+            dA = nv.sgemm(dC, w2).view(B, Ls, k, D)          # gradient per window; overlap-add back onto the rows of E
+            de = torch.zeros_like(e_flat)
+            dev = de[:B * Ls].view(B, Ls, D)
+            for i in range(k):
+                dev[:, i:] += dA[:, :Ls - i, i]
+        return de, None, None, dw, db
+
+
+def text_conv_pool(e_flat, B, Ls, conv: torch.nn.Conv2d):
+    return _TextConvPoolFn.apply(e_flat, B, Ls, conv.weight, conv.bias)

@@ -394,3 +394,86 @@ def net_fwd_bwd(x: torch.Tensor, targets: torch.Tensor, params, grads, krsc: boo
     if grads is not None:
         L.LAUNCHES[0] += 1          # two kernels per call
     return loss, logits
+
+
+# ------------------------------------------------------------------------------------------------
+# sequence models of the MNTD zoo (csrc/seq.cu), fp32
+# ------------------------------------------------------------------------------------------------
+def sgemm(A: torch.Tensor, B: torch.Tensor, bias: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+          beta: float = 0.0, relu: bool = False) -> torch.Tensor:
+    """``out[M,N] = A[M,K] @ B[K,N] (+ bias) (+ beta*out)``; ``A`` and ``B`` are 2-D fp32 CUDA tensors with any strides, so
+    a transposed operand is just ``.t()`` and overlapping rows (``as_strided``) need no copy."""
+    from ctypes import c_longlong
+    M, K = A.shape
+    K2, N = B.shape
+    assert K == K2 and A.dtype == torch.float32 and B.dtype == torch.float32
+    if out is None:
+        out = torch.empty((M, N), dtype=torch.float32, device=A.device)
+    assert out.is_contiguous() and tuple(out.shape) == (M, N)
+    L.check(L.lib().b200_sgemm(L.ptr(A), L.ptr(B), L.ptr(out), L.ptr(bias), c_int(M), c_int(N), c_int(K),
+                               c_longlong(A.stride(0)), c_longlong(A.stride(1)), c_longlong(B.stride(0)), c_longlong(B.stride(1)),
+                               c_int(N), c_float(beta), c_int(int(relu)), L.stream_ptr()), "sgemm")
+    return out
+
+
+def lstm_rec_fwd(pre: torch.Tensor, w_hh: torch.Tensor):
+    """Recurrence of one LSTM layer.  ``pre`` [B,T,4H] = x W_ih^T + b_ih + b_hh.  Returns (h [B,T,H], gates [B,T,4H], c [B,T,H])."""
+    B, T, H4 = pre.shape
+    H = H4 // 4
+    assert pre.is_contiguous() and w_hh.is_contiguous() and tuple(w_hh.shape) == (H4, H)
+    hseq = torch.empty((B, T, H), dtype=torch.float32, device=pre.device)
+    gates = torch.empty((B, T, H4), dtype=torch.float32, device=pre.device)
+    cseq = torch.empty((B, T, H), dtype=torch.float32, device=pre.device)
+    L.check(L.lib().b200_lstm_rec_fwd(L.ptr(pre), L.ptr(w_hh), L.ptr(hseq), L.ptr(gates), L.ptr(cseq), c_int(B), c_int(T), c_int(H),
+                                      L.stream_ptr()), "lstm_rec_fwd")
+    return hseq, gates, cseq
+
+
+def lstm_rec_bwd(dh: torch.Tensor, gates: torch.Tensor, cseq: torch.Tensor, w_hh: torch.Tensor) -> torch.Tensor:
+    """BPTT of one layer: gradient of the loss w.r.t. the pre-activation gates, [B,T,4H]."""
+    B, T, H = dh.shape
+    assert dh.is_contiguous() and gates.is_contiguous() and cseq.is_contiguous()
+    dgates = torch.empty_like(gates)
+    L.check(L.lib().b200_lstm_rec_bwd(L.ptr(dh), L.ptr(gates), L.ptr(cseq), L.ptr(w_hh), L.ptr(dgates), c_int(B), c_int(T), c_int(H),
+                                      L.stream_ptr()), "lstm_rec_bwd")
+    return dgates
+
+
+def mel_frontend(x: torch.Tensor, window: torch.Tensor, melfb: torch.Tensor) -> torch.Tensor:
+    """Waveforms [B,L] -> normalised log-mel features [B, 1 + L//512, n_mels] (2048-point Hann STFT, hop 512, reflect)."""
+    B, Ls = x.shape
+    assert x.is_contiguous() and x.dtype == torch.float32 and window.numel() == 2048 and melfb.shape[1] == 1025
+    out = torch.empty((B, 1 + Ls // 512, melfb.shape[0]), dtype=torch.float32, device=x.device)
+    L.check(L.lib().b200_mel_frontend(L.ptr(x), L.ptr(window), L.ptr(melfb.contiguous()), L.ptr(out), c_int(B), c_int(Ls),
+                                      c_int(melfb.shape[0]), L.stream_ptr()), "mel_frontend")
+    return out
+
+
+def gather_rows(table: torch.Tensor, idx: torch.Tensor, pad_rows: int = 0) -> torch.Tensor:
+    """``table[idx]`` for an int64 index tensor of any shape -> [idx.numel() + pad_rows, dim] (the pad rows are zero)."""
+    from ctypes import c_longlong
+    rows, dim = idx.numel(), table.shape[1]
+    assert table.is_contiguous() and table.dtype == torch.float32 and idx.dtype == torch.int64
+    out = torch.empty((rows + pad_rows, dim), dtype=torch.float32, device=table.device)
+    if pad_rows:
+        out[rows:].zero_()
+    L.check(L.lib().b200_gather_rows(L.ptr(table), L.ptr(idx.contiguous()), L.ptr(out), c_longlong(rows), c_int(dim),
+                                     c_longlong(table.shape[0]), L.stream_ptr()), "gather_rows")
+    return out
+
+
+def textcnn_pool_fwd(C: torch.Tensor, bias: torch.Tensor, feat: torch.Tensor, col: int, B: int, Ls: int, k: int) -> torch.Tensor:
+    """feat[:, col:col+N] = max over valid windows of relu(C + bias); returns the arg-max positions [B,N] (int32)."""
+    N = C.shape[1]
+    arg = torch.empty((B, N), dtype=torch.int32, device=C.device)
+    L.check(L.lib().b200_textcnn_pool_fwd(L.ptr(C), L.ptr(bias), L.ptr(feat), L.ptr(arg), c_int(B), c_int(Ls), c_int(N), c_int(k),
+                                          c_int(feat.shape[1]), c_int(col), L.stream_ptr()), "textcnn_pool_fwd")
+    return arg
+
+
+def textcnn_pool_bwd(dfeat: torch.Tensor, feat: torch.Tensor, arg: torch.Tensor, col: int, B: int, Ls: int) -> torch.Tensor:
+    N = arg.shape[1]
+    dC = torch.empty((B * Ls, N), dtype=torch.float32, device=feat.device)
+    L.check(L.lib().b200_textcnn_pool_bwd(L.ptr(dfeat), L.ptr(feat), L.ptr(arg), L.ptr(dC), c_int(B), c_int(Ls), c_int(N),
+                                          c_int(feat.shape[1]), c_int(col), L.stream_ptr()), "textcnn_pool_bwd")
+    return dC

@@ -224,6 +224,26 @@ int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geo
 int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
                     void* stream);
 
+/* ---- sequence models of the trojan-detection zoo (csrc/seq.cu), fp32 ---- */
+/* C[m][n] = sum_k A[m*sam + k*sak] * B[k*sbk + n*sbn] (+ bias[n]) (+ beta*C) (optional ReLU); transposes are strides */
+int b200_sgemm(const float* A, const float* B, float* C, const float* bias, int M, int N, int K, long long sam,
+               long long sak, long long sbk, long long sbn, int ldc, float beta, int relu, void* stream);
+/* one LSTM layer's recurrence (gate order i,f,g,o; H == 100): pre [B][T][4H] = x W_ih^T + b_ih + b_hh */
+int b200_lstm_rec_fwd(const float* pre, const float* w_hh, float* hseq, float* gates, float* cseq, int B, int T, int H,
+                      void* stream);
+int b200_lstm_rec_bwd(const float* dh, const float* gates, const float* cseq, const float* w_hh, float* dgates, int B,
+                      int T, int H, void* stream);
+/* waveform [B][L] -> (10 log10(mel power) + 50) / 50, [B][1 + L/512][n_mels]; 2048-point Hann STFT, hop 512, reflect */
+int b200_mel_frontend(const float* x, const float* window, const float* melfb, float* out, int B, int L, int n_mels,
+                      void* stream);
+int b200_gather_rows(const float* table, const int64_t* idx, float* out, long long rows, int dim, long long vocab,
+                     void* stream);
+/* bias + ReLU + max-over-time of a [B*L][N] conv-as-GEMM output (window length k), and its backward */
+int b200_textcnn_pool_fwd(const float* C, const float* bias, float* feat, int32_t* arg, int B, int L, int N, int k, int ldf,
+                          int col, void* stream);
+int b200_textcnn_pool_bwd(const float* dfeat, const float* feat, const int32_t* arg, float* dC, int B, int L, int N, int ldf,
+                          int col, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,4 +1,6 @@
 """Numerics of every native kernel against a plain PyTorch fp32 reference of the same op (GPU)."""
+import copy
+
 import pytest
 import torch
 import torch.nn.functional as F
@@ -22,6 +24,10 @@ def _act(n, c, h, w, dev, scale=1.0):
 def _rel_err(a, b):
     a, b = a.float(), b.float()
     return float((a - b).norm() / (b.norm() + 1e-12))
+
+
+def _rel(a, b):
+    return _rel_err(a.detach().cpu(), b.detach().cpu())
 
 
 CONV_CASES = [
@@ -287,3 +293,103 @@ def test_augment_and_trojan():
             xr[i, :, 5:9, 7:11] = 0.3 * pat + 0.7 * xr[i, :, 5:9, 7:11]
     nv.trojan_stamp_(x, pat, 5, 7, 0.3, mask)
     assert torch.allclose(x, xr, atol=1e-6)
+
+
+# ------------------------------------------------------------------ sequence models
+def test_sgemm_strided_variants_match_torch():
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    torch.manual_seed(0)
+    for (M, N, K) in [(70, 130, 45), (3200, 400, 40), (400, 100, 3200), (1, 400, 3200), (5, 1, 300)]:
+        A = torch.randn(M, K, device=dev)
+        B = torch.randn(K, N, device=dev)
+        bias = torch.randn(N, device=dev)
+        ref = (A.double() @ B.double()).float()
+        scale = ref.abs().max()
+        assert (nv.sgemm(A, B) - ref).abs().max() < 2e-5 * scale * (K ** 0.5)
+        assert (nv.sgemm(A.t().contiguous().t(), B.t().contiguous().t(), bias=bias) - (ref + bias)).abs().max() < 2e-5 * scale * (K ** 0.5)
+        assert (nv.sgemm(B.t(), A.t()) - ref.t()).abs().max() < 2e-5 * scale * (K ** 0.5)
+    # overlapping rows (the text-CNN im2col view) and accumulate
+    E = torch.randn(50, 8, device=dev)
+    A = E.as_strided((47, 24), (8, 1))
+    W = torch.randn(24, 10, device=dev)
+    out = torch.ones(47, 10, device=dev)
+    nv.sgemm(A, W, out=out, beta=1.0)
+    ref = torch.stack([E[t:t + 3].reshape(-1) for t in range(47)]) @ W + 1.0
+    assert torch.allclose(out, ref, atol=1e-4)
+
+
+def test_mel_frontend_matches_torch_stft_features():
+    from b200ddp.models.mntd import AudioModel
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    torch.manual_seed(1)
+    m = AudioModel()
+    x = torch.randn(5, 16000) * 0.1
+    x[0, :4000] = 0.0                          # silence: exercises the 1e-10 clamp
+    ref = m.features(x)                        # torch.stft on the CPU
+    out = nv.mel_frontend(x.to(dev), m._window.to(dev), m._mel.to(dev)).cpu()
+    assert out.shape == ref.shape == (5, 32, 40)
+    loud = ref > -0.5                          # features above -75 dB: compare tightly; below, fp32 FFT noise dominates both
+    assert (out - ref)[loud].abs().max() < 2e-3
+    assert (out - ref).abs().max() < 0.2
+
+
+def test_lstm_layers_match_torch_cpu():
+    from b200ddp.ops import functional as BF
+    dev = _dev()
+    torch.manual_seed(2)
+    ref = torch.nn.LSTM(input_size=40, hidden_size=100, num_layers=2, batch_first=True)
+    gpu = copy.deepcopy(ref).to(dev)
+    x = torch.randn(7, 32, 40)
+    xr = x.clone().requires_grad_(True)
+    out_r, _ = ref(xr)
+    wgt = torch.randn_like(out_r)
+    (out_r * wgt).sum().backward()
+    xg = x.to(dev).requires_grad_(True)
+    out_g = BF.lstm(xg, gpu)
+    (out_g * wgt.to(dev)).sum().backward()
+    torch.cuda.synchronize()
+    assert _rel(out_g, out_r) < 1e-4
+    assert _rel(xg.grad, xr.grad) < 1e-3
+    for (n, a), (_, b) in zip(ref.named_parameters(), gpu.named_parameters()):
+        assert _rel(b.grad, a.grad) < 1e-3, (n, _rel(b.grad, a.grad))
+
+
+def test_audio_and_text_models_native_paths_match_cpu():
+    from b200ddp.models.mntd import AudioModel, RTNLPModel
+    dev = _dev()
+    torch.manual_seed(3)
+    ref = AudioModel().eval()
+    gpu = copy.deepcopy(ref).to(dev)
+    x = torch.randn(4, 16000) * 0.1
+    y = torch.tensor([1, 5, 2, 7])
+    lr = ref.loss(ref(x), y)
+    lr.backward()
+    lg = gpu.loss(gpu(x.to(dev)), y.to(dev))
+    lg.backward()
+    assert abs(float(lr.detach()) - float(lg.detach())) < 2e-3
+    for (n, a), (_, b) in zip(ref.named_parameters(), gpu.named_parameters()):
+        if n == "lstm_att.bias":               # softmax is shift-invariant: this gradient is exactly zero up to rounding
+            assert float(b.grad.abs().max()) < 1e-6
+            continue
+        assert _rel(b.grad, a.grad) < 2e-2, (n, _rel(b.grad, a.grad))
+    # text CNN: token ids (gather kernel) and continuous embeddings with a gradient (query tuning)
+    ref = RTNLPModel(emb_path="").eval()
+    gpu = copy.deepcopy(ref).to(dev)
+    gpu.embed_static.embed.to(dev)
+    ids = torch.randint(1, 18000, (6, 12))
+    lab = torch.tensor([0, 1, 1, 0, 1, 0])
+    lr = ref.loss(ref(ids), lab)
+    lr.backward()
+    lg = gpu.loss(gpu(ids.to(dev)), lab.to(dev))
+    lg.backward()
+    assert abs(float(lr.detach()) - float(lg.detach())) < 1e-4
+    for (n, a), (_, b) in zip(ref.named_parameters(), gpu.named_parameters()):
+        assert _rel(b.grad, a.grad) < 1e-3, (n, _rel(b.grad, a.grad))
+    e = torch.randn(3, 1, 10, 300)
+    er = e.clone().requires_grad_(True)
+    eg = e.to(dev).requires_grad_(True)
+    ref.emb_forward(er).sum().backward()
+    gpu.emb_forward(eg).sum().backward()
+    assert _rel(eg.grad, er.grad) < 1e-3
