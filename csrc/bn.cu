@@ -85,6 +85,8 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, size_t rows, int C, const f
                 const float* __restrict__ beta, float eps, float momentum, float* __restrict__ stat /*[4][C]*/,
                 float* __restrict__ running_mean, float* __restrict__ running_var, float* __restrict__ partial,
                 unsigned* __restrict__ counters) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[2][kRL][kGroup];
   __shared__ float fin[2][kGroup];
   const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
@@ -154,6 +156,8 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, size_t rows, int C, const f
 
 __global__ void bn_eval_prep_kernel(const float* gamma, const float* beta, const float* rm, const float* rv, float eps,
                                     float* stat, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int ch = blockIdx.x * blockDim.x + threadIdx.x;
   if (ch >= C) return;
   const float rstd = rsqrtf(rv[ch] + eps), sc = gamma[ch] * rstd;
@@ -167,6 +171,8 @@ template <bool kRelu, bool kRes>
 __global__ void __launch_bounds__(kThreads)
 bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
                 __nv_bfloat16* __restrict__ y, size_t rows, int C, const float* __restrict__ stat) {
+  pdl_trigger();
+  pdl_wait();
   const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
   const int c = blockIdx.y * kGroup + v * 8;
   if (c >= C) return;
@@ -198,6 +204,8 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                      const __nv_bfloat16* __restrict__ y, size_t rows, int C, const float* __restrict__ stat,
                      float* __restrict__ sums /*[2][C]*/, float* __restrict__ dgamma, float* __restrict__ dbeta,
                      float beta_accum, float* __restrict__ partial, unsigned* __restrict__ counters) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[2][kRL][kGroup];
   const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
   const int c = blockIdx.y * kGroup + v * 8;
@@ -269,6 +277,8 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
                     const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx,
                     __nv_bfloat16* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
                     const float* __restrict__ sums) {
+  pdl_trigger();
+  pdl_wait();
   const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
   const int c = blockIdx.y * kGroup + v * 8;
   if (c >= C) return;
@@ -308,6 +318,8 @@ bn_fwd_small_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
                     __nv_bfloat16* __restrict__ y, size_t rows, int C, const float* __restrict__ gamma,
                     const float* __restrict__ beta, float eps, float momentum, float* __restrict__ stat,
                     float* __restrict__ running_mean, float* __restrict__ running_var) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[2][kRL][kGroup];
   __shared__ float fin[2][kGroup];
   const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
@@ -381,6 +393,8 @@ bn_bwd_small_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
                     const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx,
                     __nv_bfloat16* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
                     float* __restrict__ dgamma, float* __restrict__ dbeta, float beta_accum) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[2][kRL][kGroup];
   __shared__ float fin[2][kGroup];
   const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
@@ -481,7 +495,7 @@ extern "C" int b200_bn_stats(const void* x_bf16, size_t rows, int C, const float
   B200_REQUIRE((C + kGroup - 1) / kGroup <= 1024, "too many channel groups");
   B200_REQUIRE(scratch_bytes >= b200_bn_scratch_bytes(rows, C), "scratch too small (b200_bn_scratch_bytes)");
   dim3 g = bn_reduce_grid(rows, C);
-  bn_stats_kernel<<<g, kThreads, 0, (cudaStream_t)stream>>>(
+  b200_launch(bn_stats_kernel, dim3(g), dim3(kThreads), 0, (cudaStream_t)stream, 
       (const __nv_bfloat16*)x_bf16, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var,
       (float*)((char*)scratch + kCounterBytes), (unsigned*)scratch);
   B200_CHECK_LAUNCH();
@@ -491,7 +505,7 @@ extern "C" int b200_bn_stats(const void* x_bf16, size_t rows, int C, const float
 extern "C" int b200_bn_eval_prep(const float* gamma, const float* beta, const float* running_mean,
                                  const float* running_var, float eps, float* stat, int C, void* stream) {
   B200_REQUIRE(gamma && beta && running_mean && running_var && stat && C > 0, "bad argument");
-  bn_eval_prep_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(gamma, beta, running_mean, running_var, eps, stat, C);
+  b200_launch(bn_eval_prep_kernel, dim3((C + 127) / 128), dim3(128), 0, (cudaStream_t)stream, gamma, beta, running_mean, running_var, eps, stat, C);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -504,10 +518,10 @@ extern "C" int b200_bn_apply(const void* x_bf16, const void* residual_bf16, void
   cudaStream_t s = (cudaStream_t)stream;
   const __nv_bfloat16 *x = (const __nv_bfloat16*)x_bf16, *r = (const __nv_bfloat16*)residual_bf16;
   __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
-  if (relu && r) bn_apply_kernel<true, true><<<g, kThreads, 0, s>>>(x, r, y, rows, C, stat);
-  else if (relu) bn_apply_kernel<true, false><<<g, kThreads, 0, s>>>(x, r, y, rows, C, stat);
-  else if (r) bn_apply_kernel<false, true><<<g, kThreads, 0, s>>>(x, r, y, rows, C, stat);
-  else bn_apply_kernel<false, false><<<g, kThreads, 0, s>>>(x, r, y, rows, C, stat);
+  if (relu && r) b200_launch(bn_apply_kernel<true, true>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
+  else if (relu) b200_launch(bn_apply_kernel<true, false>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
+  else if (r) b200_launch(bn_apply_kernel<false, true>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
+  else b200_launch(bn_apply_kernel<false, false>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -524,11 +538,11 @@ extern "C" int b200_bn_bwd_reduce(const void* dy_bf16, const void* x_bf16, const
   float* partial = (float*)((char*)scratch + kCounterBytes);
   unsigned* counters = (unsigned*)scratch;
   if (relu)
-    bn_bwd_reduce_kernel<true><<<g, kThreads, 0, s>>>((const __nv_bfloat16*)dy_bf16, (const __nv_bfloat16*)x_bf16,
+    b200_launch(bn_bwd_reduce_kernel<true>, dim3(g), dim3(kThreads), 0, s, (const __nv_bfloat16*)dy_bf16, (const __nv_bfloat16*)x_bf16,
                                                      (const __nv_bfloat16*)y_bf16, rows, C, stat, sums, dgamma, dbeta,
                                                      beta_accum, partial, counters);
   else
-    bn_bwd_reduce_kernel<false><<<g, kThreads, 0, s>>>((const __nv_bfloat16*)dy_bf16, (const __nv_bfloat16*)x_bf16,
+    b200_launch(bn_bwd_reduce_kernel<false>, dim3(g), dim3(kThreads), 0, s, (const __nv_bfloat16*)dy_bf16, (const __nv_bfloat16*)x_bf16,
                                                       (const __nv_bfloat16*)y_bf16, rows, C, stat, sums, dgamma, dbeta,
                                                       beta_accum, partial, counters);
   B200_CHECK_LAUNCH();
@@ -546,10 +560,10 @@ extern "C" int b200_bn_bwd_apply(const void* dy_bf16, const void* x_bf16, const 
   const __nv_bfloat16 *dy = (const __nv_bfloat16*)dy_bf16, *x = (const __nv_bfloat16*)x_bf16,
                       *y = (const __nv_bfloat16*)y_bf16;
   __nv_bfloat16 *dx = (__nv_bfloat16*)dx_bf16, *dr = (__nv_bfloat16*)dres_bf16;
-  if (relu && dr) bn_bwd_apply_kernel<true, true><<<g, kThreads, 0, s>>>(dy, x, y, dx, dr, rows, C, stat, sums);
-  else if (relu) bn_bwd_apply_kernel<true, false><<<g, kThreads, 0, s>>>(dy, x, y, dx, dr, rows, C, stat, sums);
-  else if (dr) bn_bwd_apply_kernel<false, true><<<g, kThreads, 0, s>>>(dy, x, y, dx, dr, rows, C, stat, sums);
-  else bn_bwd_apply_kernel<false, false><<<g, kThreads, 0, s>>>(dy, x, y, dx, dr, rows, C, stat, sums);
+  if (relu && dr) b200_launch(bn_bwd_apply_kernel<true, true>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
+  else if (relu) b200_launch(bn_bwd_apply_kernel<true, false>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
+  else if (dr) b200_launch(bn_bwd_apply_kernel<false, true>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
+  else b200_launch(bn_bwd_apply_kernel<false, false>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -613,7 +627,7 @@ extern "C" int b200_bn_stats_noalloc(const void* x_bf16, size_t rows, int C, con
   // the tickets must be zero when the kernel starts; whatever an earlier (possibly aborted) call left goes
   B200_CHECK_CUDA(cudaMemsetAsync(scratch, 0, kCounterBytes, s));
   dim3 g = bn_reduce_grid(rows, C);
-  bn_stats_kernel<<<g, kThreads, 0, s>>>((const __nv_bfloat16*)x_bf16, rows, C, gamma, beta, eps, momentum, stat,
+  b200_launch(bn_stats_kernel, dim3(g), dim3(kThreads), 0, s, (const __nv_bfloat16*)x_bf16, rows, C, gamma, beta, eps, momentum, stat,
                                          running_mean, running_var, (float*)(scratch + kCounterBytes),
                                          (unsigned*)scratch);
   B200_CHECK_LAUNCH();
@@ -632,7 +646,7 @@ extern "C" int b200_bn_fwd_fused(const void* x_bf16, const void* residual_bf16, 
   cudaStream_t s = (cudaStream_t)stream;
   const __nv_bfloat16 *x = (const __nv_bfloat16*)x_bf16, *r = (const __nv_bfloat16*)residual_bf16;
   __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
-#define B200_BNF(R, S) bn_fwd_small_kernel<R, S><<<g, kThreads, 0, s>>>(x, r, y, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var)
+#define B200_BNF(R, S) b200_launch(bn_fwd_small_kernel<R, S>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var)
   if (relu && r) B200_BNF(true, true);
   else if (relu) B200_BNF(true, false);
   else if (r) B200_BNF(false, true);
@@ -653,7 +667,7 @@ extern "C" int b200_bn_bwd_fused(const void* dy_bf16, const void* x_bf16, const 
   cudaStream_t s = (cudaStream_t)stream;
   const __nv_bfloat16 *dy = (const __nv_bfloat16*)dy_bf16, *x = (const __nv_bfloat16*)x_bf16, *y = (const __nv_bfloat16*)y_bf16;
   __nv_bfloat16 *dx = (__nv_bfloat16*)dx_bf16, *dr = (__nv_bfloat16*)dres_bf16;
-#define B200_BNB(R, S) bn_bwd_small_kernel<R, S><<<g, kThreads, 0, s>>>(dy, x, y, dx, dr, rows, C, stat, dgamma, dbeta, beta_accum)
+#define B200_BNB(R, S) b200_launch(bn_bwd_small_kernel<R, S>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, dgamma, dbeta, beta_accum)
   if (relu && dr) B200_BNB(true, true);
   else if (relu) B200_BNB(true, false);
   else if (dr) B200_BNB(false, true);

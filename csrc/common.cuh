@@ -59,6 +59,34 @@ static inline unsigned b200_grid_for(size_t work_items, int threads, int per_sm)
 }
 
 // ------------------------------------------------------------------------------------------
+// Programmatic dependent launch.  Kernels started with b200_launch() may be scheduled while the previous kernel
+// of the stream is still draining (its launch latency and prologue overlap that tail); such a kernel calls
+// pdl_wait() before it touches memory its predecessor writes, and every one of its CTAs that does not exit at once
+// executes pdl_wait(), so completion stays transitive along the stream.  B200DDP_PDL=0 turns the attribute off.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool b200_pdl_enabled();
+
+template <typename... KArgs, typename... Args>
+static inline cudaError_t b200_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                      Args&&... args) {
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = b200_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<Args&&>(args)...);
+}
+
+// ------------------------------------------------------------------------------------------
 // device helpers
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {

@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(THREADS, 1)
 conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUtensorMap tmA,
                const __grid_constant__ CUtensorMap tmB) {
   using C = Cfg<MODE, BN>;
+  pdl_trigger();                  // the next kernel of the stream may be scheduled now; it waits for us in its own pdl_wait()
   const uint32_t m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   if (MODE == MODE_WGRAD && p.cpt != 0) {
     // N tile = columns (r,s,ci): drop tiles whose taps never see a real pixel (their dW is exactly 0)
@@ -169,6 +170,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();                     // barriers, TMEM and descriptors are set up; from here on we read the previous kernel's output
   STAMP(1, 0);
 
   if (warp < 4) {
@@ -498,13 +500,22 @@ int launch_zc(const ConvParams& p, const CUtensorMap& tmA, const CUtensorMap& tm
   cfg.blockDim = dim3(THREADS, 1, 1);
   cfg.dynamicSmemBytes = C::SMEM_BYTES;
   cfg.stream = s;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = 1;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = ZC;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (ZC > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 1;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = ZC;
+    ++na;
+  }
+  if (b200_pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = ZC > 1 ? 1 : 0;
+  cfg.numAttrs = na;
   B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<MODE, BN, ZC>, p, tmA, tmB));
   return 0;
 }

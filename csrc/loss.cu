@@ -31,6 +31,8 @@ __global__ void __launch_bounds__(128)
 softmax_xent_kernel(const T* __restrict__ logits, const int64_t* __restrict__ targets, int rows, int cols,
                     float* __restrict__ row_loss, float* __restrict__ loss_mean, T* __restrict__ dlogits,
                     float grad_scale, unsigned int* __restrict__ counter) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int row = blockIdx.x * 4 + w;
   if (row < rows) {
@@ -79,6 +81,8 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 bce_logits_kernel(const T* __restrict__ x, const float* __restrict__ t, int n, float* __restrict__ loss_mean,
                   T* __restrict__ dx, float grad_scale) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float red[32];
   float s = 0.f;
   for (int i = threadIdx.x; i < n; i += blockDim.x) {
@@ -94,6 +98,8 @@ template <typename T>
 __global__ void __launch_bounds__(128)
 eval_count_kernel(const T* __restrict__ logits, const int64_t* __restrict__ targets, int rows, int cols,
                   int* __restrict__ correct, float* __restrict__ nll_sum) {
+  pdl_trigger();
+  pdl_wait();
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int row = blockIdx.x * 4 + w;
   if (row >= rows) return;
@@ -127,10 +133,10 @@ extern "C" int b200_softmax_xent(const void* logits, int dtype, const int64_t* t
   const unsigned grid = (rows + 3) / 4;
   cudaStream_t s = (cudaStream_t)stream;
   if (dtype == B200_DTYPE_F32)
-    softmax_xent_kernel<float><<<grid, 128, 0, s>>>((const float*)logits, targets, rows, cols, row_loss, loss_mean,
+    b200_launch(softmax_xent_kernel<float>, dim3(grid), dim3(128), 0, s, (const float*)logits, targets, rows, cols, row_loss, loss_mean,
                                                    (float*)dlogits, grad_scale, scratch_counter);
   else if (dtype == B200_DTYPE_BF16)
-    softmax_xent_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>((const __nv_bfloat16*)logits, targets, rows, cols, row_loss,
+    b200_launch(softmax_xent_kernel<__nv_bfloat16>, dim3(grid), dim3(128), 0, s, (const __nv_bfloat16*)logits, targets, rows, cols, row_loss,
                                                            loss_mean, (__nv_bfloat16*)dlogits, grad_scale,
                                                            scratch_counter);
   else {
@@ -146,9 +152,9 @@ extern "C" int b200_bce_logits(const void* logits, int dtype, const float* targe
   B200_REQUIRE(logits && targets && loss_mean && n > 0, "bad argument");
   cudaStream_t s = (cudaStream_t)stream;
   if (dtype == B200_DTYPE_F32)
-    bce_logits_kernel<float><<<1, 256, 0, s>>>((const float*)logits, targets, n, loss_mean, (float*)dlogits, grad_scale);
+    b200_launch(bce_logits_kernel<float>, dim3(1), dim3(256), 0, s, (const float*)logits, targets, n, loss_mean, (float*)dlogits, grad_scale);
   else
-    bce_logits_kernel<__nv_bfloat16><<<1, 256, 0, s>>>((const __nv_bfloat16*)logits, targets, n, loss_mean,
+    b200_launch(bce_logits_kernel<__nv_bfloat16>, dim3(1), dim3(256), 0, s, (const __nv_bfloat16*)logits, targets, n, loss_mean,
                                                       (__nv_bfloat16*)dlogits, grad_scale);
   B200_CHECK_LAUNCH();
   return 0;
@@ -160,9 +166,9 @@ extern "C" int b200_eval_count(const void* logits, int dtype, const int64_t* tar
   const unsigned grid = (rows + 3) / 4;
   cudaStream_t s = (cudaStream_t)stream;
   if (dtype == B200_DTYPE_F32)
-    eval_count_kernel<float><<<grid, 128, 0, s>>>((const float*)logits, targets, rows, cols, correct_out, nll_sum_out);
+    b200_launch(eval_count_kernel<float>, dim3(grid), dim3(128), 0, s, (const float*)logits, targets, rows, cols, correct_out, nll_sum_out);
   else
-    eval_count_kernel<__nv_bfloat16><<<grid, 128, 0, s>>>((const __nv_bfloat16*)logits, targets, rows, cols,
+    b200_launch(eval_count_kernel<__nv_bfloat16>, dim3(grid), dim3(128), 0, s, (const __nv_bfloat16*)logits, targets, rows, cols,
                                                          correct_out, nll_sum_out);
   B200_CHECK_LAUNCH();
   return 0;

@@ -13,6 +13,8 @@ template <bool kShadow, bool kZero, bool kNesterov>
 __global__ void __launch_bounds__(256)
 sgd_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ m, uint2* __restrict__ shadow,
            size_t n4, float lr, float momentum, float one_minus_damp, float wd, float gscale) {
+  pdl_trigger();
+  pdl_wait();
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 pv = p[i], gv = g[i];
@@ -50,6 +52,8 @@ __global__ void __launch_bounds__(256)
 adam_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__ m, float4* __restrict__ v,
             uint2* __restrict__ shadow, size_t n4, float lr, float b1, float b2, float eps, float wd,
             const int* __restrict__ step_dev, float gscale) {
+  pdl_trigger();
+  pdl_wait();
   const float t = (float)(*step_dev);
   const float bc1 = 1.f - powf(b1, t), bc2 = 1.f - powf(b2, t);
   const float step_size = lr / bc1, inv_sqrt_bc2 = rsqrtf(bc2);
@@ -80,9 +84,13 @@ adam_kernel(float4* __restrict__ p, float4* __restrict__ g, float4* __restrict__
   }
 }
 
-__global__ void step_inc_kernel(int* s) { *s += 1; }
+__global__ void step_inc_kernel(int* s) {
+  pdl_trigger();
+  pdl_wait(); *s += 1; }
 
 __global__ void __launch_bounds__(256) cast_kernel(const float4* __restrict__ src, uint2* __restrict__ dst, size_t n4) {
+  pdl_trigger();
+  pdl_wait();
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 a = src[i];
@@ -110,7 +118,7 @@ extern "C" int b200_sgd_momentum(float* p, float* g, float* m, void* shadow_bf16
   float4 *p4 = (float4*)p, *g4 = (float4*)g, *m4 = (float4*)m;
   uint2* sh = (uint2*)shadow_bf16;
   const float omd = 1.f - dampening;
-#define B200_SGD(S, Z, N) sgd_kernel<S, Z, N><<<grid, 256, 0, s>>>(p4, g4, m4, sh, n4, lr, momentum, omd, weight_decay, grad_scale)
+#define B200_SGD(S, Z, N) b200_launch(sgd_kernel<S, Z, N>, dim3(grid), dim3(256), 0, s, p4, g4, m4, sh, n4, lr, momentum, omd, weight_decay, grad_scale)
   const bool S = sh != nullptr, Z = zero_grad != 0, N = nesterov != 0;
   if (S && Z && N) B200_SGD(true, true, true);
   else if (S && Z) B200_SGD(true, true, false);
@@ -136,7 +144,7 @@ extern "C" int b200_adam(float* p, float* g, float* m, float* v, void* shadow_bf
   cudaStream_t s = (cudaStream_t)stream;
   uint2* sh = (uint2*)shadow_bf16;
 #define B200_ADAM(S, Z) \
-  adam_kernel<S, Z><<<grid, 256, 0, s>>>((float4*)p, (float4*)g, (float4*)m, (float4*)v, sh, n4, lr, beta1, beta2, eps, weight_decay, step_dev, grad_scale)
+  b200_launch(adam_kernel<S, Z>, dim3(grid), dim3(256), 0, s, (float4*)p, (float4*)g, (float4*)m, (float4*)v, sh, n4, lr, beta1, beta2, eps, weight_decay, step_dev, grad_scale)
   const bool S = sh != nullptr, Z = zero_grad != 0;
   if (S && Z) B200_ADAM(true, true);
   else if (S) B200_ADAM(true, false);
@@ -149,7 +157,7 @@ extern "C" int b200_adam(float* p, float* g, float* m, float* v, void* shadow_bf
 
 extern "C" int b200_step_inc(int* step_dev, void* stream) {
   B200_REQUIRE(step_dev, "null step");
-  step_inc_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(step_dev);
+  b200_launch(step_inc_kernel, dim3(1), dim3(1), 0, (cudaStream_t)stream, step_dev);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -158,7 +166,7 @@ extern "C" int b200_cast_f32_to_bf16(const float* src, void* dst_bf16, size_t n,
   B200_REQUIRE(src && dst_bf16, "null argument");
   B200_REQUIRE(n % 4 == 0, "n must be a multiple of 4");
   if (n == 0) return 0;
-  cast_kernel<<<b200_grid_for(n / 4, 256, 8), 256, 0, (cudaStream_t)stream>>>((const float4*)src, (uint2*)dst_bf16, n / 4);
+  b200_launch(cast_kernel, dim3(b200_grid_for(n / 4, 256, 8)), dim3(256), 0, (cudaStream_t)stream, (const float4*)src, (uint2*)dst_bf16, n / 4);
   B200_CHECK_LAUNCH();
   return 0;
 }

@@ -14,6 +14,8 @@ namespace {
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ amax,
                    int N, int H, int W, int C, int Ho, int Wo, int k, int stride, int pad) {
+  pdl_trigger();
+  pdl_wait();
   const int CV = C / 8;
   const size_t total = (size_t)N * Ho * Wo * CV;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -55,6 +57,8 @@ __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ amax,
                    __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int k, int stride,
                    int pad) {
+  pdl_trigger();
+  pdl_wait();
   const int CV = C / 8;
   const size_t total = (size_t)N * H * W * CV;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -94,6 +98,8 @@ maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restri
 // x [N][HW][C] -> y [N][C] (mean over HW); one thread per (n, 8ch)
 __global__ void __launch_bounds__(256)
 avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int HW, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int CV = C / 8;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= N * CV) return;
@@ -115,6 +121,8 @@ avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
 
 __global__ void __launch_bounds__(256)
 avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int HW, int C) {
+  pdl_trigger();
+  pdl_wait();
   const int CV = C / 8;
   const size_t total = (size_t)N * HW * CV;
   const float inv = 1.f / (float)HW;
@@ -131,6 +139,8 @@ avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restri
 
 __global__ void __launch_bounds__(256)
 relu_bwd_kernel(const bf16x8* __restrict__ dy, const bf16x8* __restrict__ y, bf16x8* __restrict__ dx, size_t n8) {
+  pdl_trigger();
+  pdl_wait();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
     float g[8], v[8];
     bf16x8_to_float(dy[i], g);
@@ -146,6 +156,8 @@ __global__ void __launch_bounds__(256)
 augment_kernel(const uint8_t* __restrict__ img, const int32_t* __restrict__ offsets, void* __restrict__ out, int N,
                int H, int W, int C, int C_out, int pad, const float* __restrict__ mean,
                const float* __restrict__ inv_std, int layout) {
+  pdl_trigger();
+  pdl_wait();
   const size_t total = (size_t)N * H * W;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int w = (int)(i % W);
@@ -180,6 +192,8 @@ augment_kernel(const uint8_t* __restrict__ img, const int32_t* __restrict__ offs
 __global__ void __launch_bounds__(256)
 trojan_stamp_kernel(float* __restrict__ x, int N, int C, int H, int W, const float* __restrict__ pattern, int PC,
                     int ph, int pw, int loc_h, int loc_w, float alpha, const uint8_t* __restrict__ mask) {
+  pdl_trigger();
+  pdl_wait();
   const size_t total = (size_t)N * PC * ph * pw;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int s = (int)(i % pw);
@@ -198,6 +212,8 @@ trojan_stamp_kernel(float* __restrict__ x, int N, int C, int H, int W, const flo
 // dbias[c] += sum_rows dy[row][c]   (bias gradient of conv / linear layers; fp32 atomics into the arena)
 __global__ void __launch_bounds__(256)
 colsum_accum_kernel(const __nv_bfloat16* __restrict__ dy, size_t rows, int C, int c_valid, float* __restrict__ out) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sm[32][64];
   const int v = threadIdx.x & 7, rl = threadIdx.x >> 3;
   const int c = blockIdx.y * 64 + v * 8;
@@ -232,7 +248,7 @@ extern "C" int b200_maxpool_fwd(const void* x, void* y, uint8_t* argmax, int N, 
   B200_REQUIRE(C % 8 == 0 && k * k <= 255 && stride > 0, "C must be a multiple of 8");
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const size_t total = (size_t)N * Ho * Wo * (C / 8);
-  maxpool_fwd_kernel<<<b200_grid_for(total, 256, 8), 256, 0, (cudaStream_t)stream>>>(
+  b200_launch(maxpool_fwd_kernel, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 
       (const __nv_bfloat16*)x, (__nv_bfloat16*)y, argmax, N, H, W, C, Ho, Wo, k, stride, pad);
   B200_CHECK_LAUNCH();
   return 0;
@@ -244,7 +260,7 @@ extern "C" int b200_maxpool_bwd(const void* dy, const uint8_t* argmax, void* dx,
   B200_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const size_t total = (size_t)N * H * W * (C / 8);
-  maxpool_bwd_kernel<<<b200_grid_for(total, 256, 8), 256, 0, (cudaStream_t)stream>>>(
+  b200_launch(maxpool_bwd_kernel, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 
       (const __nv_bfloat16*)dy, argmax, (__nv_bfloat16*)dx, N, H, W, C, Ho, Wo, k, stride, pad);
   B200_CHECK_LAUNCH();
   return 0;
@@ -253,7 +269,7 @@ extern "C" int b200_maxpool_bwd(const void* dy, const uint8_t* argmax, void* dx,
 extern "C" int b200_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {
   B200_REQUIRE(x && y && C % 8 == 0, "bad argument");
   const int total = N * (C / 8);
-  avgpool_fwd_kernel<<<(total + 255) / 256, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, HW, C);
+  b200_launch(avgpool_fwd_kernel, dim3((total + 255) / 256), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, HW, C);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -261,7 +277,7 @@ extern "C" int b200_avgpool_fwd(const void* x, void* y, int N, int HW, int C, vo
 extern "C" int b200_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream) {
   B200_REQUIRE(dy && dx && C % 8 == 0, "bad argument");
   const size_t total = (size_t)N * HW * (C / 8);
-  avgpool_bwd_kernel<<<b200_grid_for(total, 256, 8), 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, HW, C);
+  b200_launch(avgpool_bwd_kernel, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, HW, C);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -269,7 +285,7 @@ extern "C" int b200_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, 
 extern "C" int b200_relu_bwd(const void* dy, const void* y, void* dx, size_t n, void* stream) {
   B200_REQUIRE(dy && y && dx && n % 8 == 0, "n must be a multiple of 8");
   if (n == 0) return 0;
-  relu_bwd_kernel<<<b200_grid_for(n / 8, 256, 8), 256, 0, (cudaStream_t)stream>>>((const bf16x8*)dy, (const bf16x8*)y, (bf16x8*)dx, n / 8);
+  b200_launch(relu_bwd_kernel, dim3(b200_grid_for(n / 8, 256, 8)), dim3(256), 0, (cudaStream_t)stream, (const bf16x8*)dy, (const bf16x8*)y, (bf16x8*)dx, n / 8);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -280,7 +296,7 @@ extern "C" int b200_augment(const uint8_t* img_u8, const int32_t* offsets, void*
   B200_REQUIRE(layout == 0 || (layout == 1 && C_out == C), "layout 1 (NCHW fp32) needs C_out == C");
   B200_REQUIRE(C_out >= C, "C_out < C");
   const size_t total = (size_t)N * H * W;
-  augment_kernel<<<b200_grid_for(total, 256, 8), 256, 0, (cudaStream_t)stream>>>(img_u8, offsets, out, N, H, W, C, C_out, pad, mean, inv_std, layout);
+  b200_launch(augment_kernel, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, img_u8, offsets, out, N, H, W, C, C_out, pad, mean, inv_std, layout);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -292,7 +308,7 @@ extern "C" int b200_trojan_stamp(float* x, int N, int C, int H, int W, const flo
   B200_REQUIRE(pattern_channels == 1 || pattern_channels == C, "pattern channels must be 1 or C");
   const size_t total = (size_t)N * pattern_channels * p_h * p_w;
   if (total == 0) return 0;
-  trojan_stamp_kernel<<<b200_grid_for(total, 256, 8), 256, 0, (cudaStream_t)stream>>>(x, N, C, H, W, pattern, pattern_channels, p_h, p_w, loc_h, loc_w, alpha, mask);
+  b200_launch(trojan_stamp_kernel, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, x, N, C, H, W, pattern, pattern_channels, p_h, p_w, loc_h, loc_w, alpha, mask);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -304,7 +320,7 @@ extern "C" int b200_colsum_accum(const void* dy_bf16, size_t rows, int C, int c_
   if (rb < 1) rb = 1;
   if (rb > 64) rb = 64;
   dim3 grid((unsigned)rb, (unsigned)((C + 63) / 64), 1);
-  colsum_accum_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)dy_bf16, rows, C, c_valid, out);
+  b200_launch(colsum_accum_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)dy_bf16, rows, C, c_valid, out);
   B200_CHECK_LAUNCH();
   return 0;
 }

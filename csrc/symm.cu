@@ -8,8 +8,18 @@
 #include <unistd.h>
 
 #include "common.cuh"
+#include <stdlib.h>
 
 static thread_local char g_err[1024] = "";
+
+bool b200_pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("B200DDP_PDL");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
 
 void b200_set_error(const char* fmt, ...) {
   va_list ap;
