@@ -82,6 +82,16 @@ class ResNet(nn.Module):
             elif isinstance(m, nn.BatchNorm2d):
                 nn.init.constant_(m.weight, 1)
                 nn.init.constant_(m.bias, 0)
+        # every conv here feeds exactly one BatchNorm: let the conv epilogue produce its batch statistics
+        self.conv1.fuse_bn_stats(self.bn1)
+        for m in self.modules():
+            for i in (1, 2, 3):
+                conv, bn = getattr(m, "conv%d" % i, None), getattr(m, "bn%d" % i, None)
+                if m is not self and isinstance(conv, bnn.Conv2d) and isinstance(bn, bnn.BatchNorm2d):
+                    conv.fuse_bn_stats(bn)
+            ds = getattr(m, "downsample", None)
+            if isinstance(ds, nn.Sequential):
+                ds[0].fuse_bn_stats(ds[1])
 
     def _make_layer(self, block, planes, blocks, stride=1):
         downsample = None

@@ -15,6 +15,10 @@ import torch.nn as nn
 from ..ops import functional as BF
 
 
+# B200DDP_FUSE_BN_STATS=0: BatchNorm always makes its own statistics pass
+_FUSE_BN_STATS = [__import__("os").environ.get("B200DDP_FUSE_BN_STATS", "1") != "0"]
+
+
 class Conv2d(nn.Conv2d):
     """conv (+bias) with an optional fused ReLU epilogue."""
 
@@ -23,10 +27,35 @@ class Conv2d(nn.Conv2d):
         if self.stride[0] != self.stride[1] or self.padding[0] != self.padding[1]:
             raise ValueError("b200ddp.nn.Conv2d supports symmetric stride/padding only")
         self.fused_relu = relu
+        self._bn_pair = None          # weakref to the BatchNorm2d that consumes this conv's output (fuse_bn_stats)
+        self._bn_sums = None
+
+    def fuse_bn_stats(self, bn: "BatchNorm2d"):
+        """Declare that ``bn`` normalises exactly this conv's output.  In training mode on CUDA the conv epilogue then
+        accumulates the per-channel sum / sum of squares (fp32) and ``bn`` skips its own statistics pass over the tensor."""
+        import weakref
+        if self.bias is not None or self.fused_relu:
+            raise ValueError("fuse_bn_stats needs a conv without bias and without fused ReLU")
+        self._bn_pair = weakref.ref(bn)
+        return self
 
     def forward(self, x):
-        if x.is_cuda:
-            x = BF.as_activation(x)
+        if not x.is_cuda:
+            return BF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0], self.fused_relu)
+        x = BF.as_activation(x)
+        bn = self._bn_pair() if self._bn_pair is not None else None
+        if bn is not None and self.training and bn.training and _FUSE_BN_STATS[0]:
+            n, _, h, w = x.shape
+            ho = (h + 2 * self.padding[0] - self.kernel_size[0]) // self.stride[0] + 1
+            wo = (w + 2 * self.padding[0] - self.kernel_size[1]) // self.stride[0] + 1
+            rows = n * ho * wo
+            if rows > BF.nv.BN_SMALL_ROWS:      # small tensors: BN's single-launch kernel is cheaper than finalize + apply
+                kp = BF.ceil8(self.out_channels)
+                if self._bn_sums is None or self._bn_sums.device != x.device:
+                    self._bn_sums = torch.zeros(2 * kp, dtype=torch.float32, device=x.device)   # zero at rest
+                y = BF.conv2d(x, self.weight, None, self.stride[0], self.padding[0], False, self._bn_sums)
+                y._b200_bn_sums = self._bn_sums
+                return y
         return BF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0], self.fused_relu)
 
 
@@ -85,6 +114,7 @@ class BatchNorm2d(nn.BatchNorm2d):
 
     def forward(self, x, residual: Optional[torch.Tensor] = None):
         training = self.training or not self.track_running_stats
+        presummed = getattr(x, "_b200_bn_sums", None) if (x.is_cuda and self.training) else None
         if x.is_cuda:
             x = BF.as_activation(x)
             if residual is not None:
@@ -93,7 +123,8 @@ class BatchNorm2d(nn.BatchNorm2d):
                     and not _DEFER_BN_COUNTER[0]):
                 self.num_batches_tracked.add_(1)
         return BF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, training,
-                             self.momentum if self.momentum is not None else 0.1, self.eps, self.fused_relu, residual)
+                             self.momentum if self.momentum is not None else 0.1, self.eps, self.fused_relu, residual,
+                             presummed)
 
 
 class MaxPool2d(nn.Module):

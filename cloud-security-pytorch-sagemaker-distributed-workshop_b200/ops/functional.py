@@ -97,12 +97,12 @@ def _deposit(param: torch.Tensor, grad_native: Optional[torch.Tensor], producer)
 # ------------------------------------------------------------------------------------------------
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, pad, relu):
+    def forward(ctx, x, weight, bias, stride, pad, relu, bn_sums=None):
         K, C, R, S = weight.shape
         Cp, Kp = x.shape[1], ceil8(K)
         w = conv_weight_shadow(weight, Cp, Kp)
         b = _pad_vec(bias, Kp)
-        y = nv.conv_fwd(x, w, b, stride, pad, relu)
+        y = nv.conv_fwd(x, w, b, stride, pad, relu, bn_sums)
         ctx.save_for_backward(x, w, y if relu else None)
         ctx.meta = (weight, bias, stride, pad, relu, K, C, R, S, Cp, Kp)
         return y
@@ -140,14 +140,16 @@ class _Conv2dFn(torch.autograd.Function):
             else:
                 db = torch.zeros(K, dtype=torch.float32, device=dy.device)
                 nv.colsum_accum_(db, dy, K)
-        return dx, dw, db, None, None, None
+        return dx, dw, db, None, None, None, None
 
 
-def conv2d(x, weight, bias=None, stride=1, padding=0, relu=False):
+def conv2d(x, weight, bias=None, stride=1, padding=0, relu=False, bn_sums=None):
+    """``bn_sums`` (CUDA only; fp32 [2, ceil8(Cout)], zero on entry, needs bias=None and relu=False): the conv epilogue also
+    accumulates the output's per-channel sum / sum of squares there -- see ``batch_norm(..., presummed=)``."""
     if not x.is_cuda:
         y = F.conv2d(x, weight, bias, stride=stride, padding=padding)
         return F.relu(y) if relu else y
-    return _Conv2dFn.apply(x, weight, bias, int(stride), int(padding), bool(relu))
+    return _Conv2dFn.apply(x, weight, bias, int(stride), int(padding), bool(relu), bn_sums)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -219,9 +221,13 @@ def linear(x, weight, bias=None, relu=False, nhwc_from=None):
 # ------------------------------------------------------------------------------------------------
 class _BatchNormFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu):
+    def forward(ctx, x, residual, gamma, beta, running_mean, running_var, training, momentum, eps, relu, presummed=None):
         rows = x.numel() // x.shape[1]
-        if training and rows <= nv.BN_SMALL_ROWS:
+        if training and presummed is not None:
+            # the producing conv already accumulated sum / sum of squares per channel in its epilogue
+            stat = nv.bn_finalize(presummed, rows, gamma.detach(), beta.detach(), eps, momentum, running_mean, running_var)
+            y = nv.bn_apply(x, residual, stat, relu)
+        elif training and rows <= nv.BN_SMALL_ROWS:
             y, stat = nv.bn_fwd_fused(x, residual, gamma.detach(), beta.detach(), eps, momentum, running_mean, running_var, relu)
         else:
             if training:
@@ -251,23 +257,24 @@ class _BatchNormFn(torch.autograd.Function):
                 dx, dres, _ = nv.bn_bwd(dy, x, y, stat, relu, has_res, gs.flat[:C], bs.flat[:C], 1.0)
             gs.done()
             bs.done()
-            return dx, dres, None, None, None, None, None, None, None, None
+            return dx, dres, None, None, None, None, None, None, None, None, None
         if small:
             dg, db = torch.zeros(C, device=x.device), torch.zeros(C, device=x.device)
             dx, dres = nv.bn_bwd_fused(dy, x, y, stat, relu, has_res, dg, db, 0.0)
-            return dx, dres, dg, db, None, None, None, None, None, None
+            return dx, dres, dg, db, None, None, None, None, None, None, None
         dx, dres, sums = nv.bn_bwd(dy, x, y, stat, relu, has_res)
-        return dx, dres, sums[1].clone(), sums[0].clone(), None, None, None, None, None, None
+        return dx, dres, sums[1].clone(), sums[0].clone(), None, None, None, None, None, None, None
 
 
-def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum=0.1, eps=1e-5, relu=False, residual=None):
+def batch_norm(x, gamma, beta, running_mean, running_var, training, momentum=0.1, eps=1e-5, relu=False, residual=None,
+               presummed=None):
     if not x.is_cuda:
         y = F.batch_norm(x, running_mean, running_var, gamma, beta, training, momentum, eps)
         if residual is not None:
             y = y + residual
         return F.relu(y) if relu else y
     return _BatchNormFn.apply(x, residual, gamma, beta, running_mean, running_var, bool(training), float(momentum),
-                              float(eps), bool(relu))
+                              float(eps), bool(relu), presummed)
 
 
 # ------------------------------------------------------------------------------------------------

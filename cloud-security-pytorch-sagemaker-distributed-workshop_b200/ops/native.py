@@ -81,14 +81,20 @@ def conv_out_hw(H, W, R, S, stride, pad) -> Tuple[int, int]:
 
 
 def conv_fwd(x: torch.Tensor, w_krsc: torch.Tensor, bias: Optional[torch.Tensor], stride: int, pad: int,
-             relu: bool) -> torch.Tensor:
-    """x [N,C,H,W] cl bf16, w [K,R,S,C] bf16 contiguous -> y [N,K,Ho,Wo] cl bf16."""
+             relu: bool, bn_sums: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x [N,C,H,W] cl bf16, w [K,R,S,C] bf16 contiguous -> y [N,K,Ho,Wo] cl bf16.  With ``bn_sums`` (fp32 [2,K], zero on
+    entry; no bias / ReLU) the epilogue also accumulates the per-channel sum and sum of squares of the output."""
     N, C, H, W = x.shape
     K, R, S, C2 = w_krsc.shape
     assert C2 == C and _cl_ok(x) and w_krsc.is_contiguous()
     Ho, Wo = conv_out_hw(H, W, R, S, stride, pad)
     y = empty_act(N, K, Ho, Wo, x.device)
     g = _geom(N, H, W, C, K, R, S, stride, pad)
+    if bn_sums is not None:
+        assert bias is None and not relu and bn_sums.numel() == 2 * K and bn_sums.dtype == torch.float32
+        L.check(L.lib().b200_conv_fwd_stats(L.ptr(x), L.ptr(w_krsc), L.ptr(y), byref(g), L.ptr(bn_sums), L.stream_ptr()),
+                "conv_fwd_stats")
+        return y
     L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w_krsc), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
                                   L.stream_ptr()), "conv_fwd")
     return y
@@ -162,6 +168,17 @@ def bn_stats(x: torch.Tensor, gamma, beta, eps: float, momentum: float, running_
     L.check(L.lib().b200_bn_stats(L.ptr(x), c_size_t(rows), c_int(C), L.ptr(gamma), L.ptr(beta), c_float(eps),
                                   c_float(momentum), L.ptr(stat), L.ptr(running_mean), L.ptr(running_var), L.ptr(sc),
                                   c_size_t(sc.numel()), L.stream_ptr()), "bn_stats")
+    return stat
+
+
+def bn_finalize(sums: torch.Tensor, rows: int, gamma, beta, eps: float, momentum: float, running_mean, running_var) -> torch.Tensor:
+    """Training-mode statistics from the per-channel sums a conv epilogue accumulated (``conv_fwd(..., bn_sums=)``);
+    leaves ``sums`` zero for the next forward."""
+    C = gamma.numel()
+    stat = torch.empty((4, C), dtype=torch.float32, device=gamma.device)
+    L.check(L.lib().b200_bn_finalize(L.ptr(sums), c_size_t(rows), c_int(C), L.ptr(gamma), L.ptr(beta), c_float(eps),
+                                     c_float(momentum), L.ptr(stat), L.ptr(running_mean), L.ptr(running_var), L.stream_ptr()),
+            "bn_finalize")
     return stat
 
 

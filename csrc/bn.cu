@@ -154,6 +154,32 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, size_t rows, int C, const f
   }
 }
 
+// sums[0..C) / sums[C..2C) (accumulated by the conv epilogue) -> stat, running statistics; sums are left zero
+__global__ void bn_finalize_kernel(float* __restrict__ sums, size_t rows, int C, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float eps, float momentum, float* __restrict__ stat,
+                                   float* __restrict__ running_mean, float* __restrict__ running_var) {
+  pdl_trigger();
+  pdl_wait();
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ch >= C) return;
+  const float inv_n = 1.f / (float)rows;
+  const float mean = sums[ch] * inv_n;
+  const float var = fmaxf(sums[C + ch] * inv_n - mean * mean, 0.f);
+  sums[ch] = 0.f;
+  sums[C + ch] = 0.f;
+  const float rstd = rsqrtf(var + eps);
+  const float sc = gamma[ch] * rstd;
+  stat[ch] = mean;
+  stat[C + ch] = rstd;
+  stat[2 * C + ch] = sc;
+  stat[3 * C + ch] = beta[ch] - mean * sc;
+  if (running_mean != nullptr) {
+    const float unbiased = rows > 1 ? var * (float)rows / (float)(rows - 1) : var;
+    running_mean[ch] = (1.f - momentum) * running_mean[ch] + momentum * mean;
+    running_var[ch] = (1.f - momentum) * running_var[ch] + momentum * unbiased;
+  }
+}
+
 __global__ void bn_eval_prep_kernel(const float* gamma, const float* beta, const float* rm, const float* rv, float eps,
                                     float* stat, int C) {
   pdl_trigger();
@@ -673,6 +699,17 @@ extern "C" int b200_bn_bwd_fused(const void* dy_bf16, const void* x_bf16, const 
   else if (dr) B200_BNB(false, true);
   else B200_BNB(false, false);
 #undef B200_BNB
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// Training-mode BN statistics from per-channel sums that the conv epilogue accumulated (b200_conv_fwd_stats): writes
+// stat[4][C] = mean, rstd, gamma*rstd, beta - mean*gamma*rstd, updates the running statistics, zeroes `sums`.
+extern "C" int b200_bn_finalize(float* sums, size_t rows, int C, const float* gamma, const float* beta, float eps,
+                                float momentum, float* stat, float* running_mean, float* running_var, void* stream) {
+  B200_REQUIRE(sums && gamma && beta && stat && rows > 0 && C > 0, "bad bn_finalize argument");
+  b200_launch(bn_finalize_kernel, dim3((C + 127) / 128), dim3(128), 0, (cudaStream_t)stream, sums, rows, C, gamma, beta, eps,
+              momentum, stat, running_mean, running_var);
   B200_CHECK_LAUNCH();
   return 0;
 }

@@ -57,6 +57,7 @@ struct ConvParams {
   const __nv_bfloat16* dy;   // output-side tensor (DGRAD/WGRAD)
   void* out;                 // FWD: y bf16 [M][Cout]; DGRAD: dx bf16 [M][Cin]; WGRAD: dw fp32 [Cout][R*S*Cin]
   const float* bias;         // FWD only, may be null
+  float* bn_sums;            // FWD only, may be null: per-channel sum [gemm_n] and sum of squares [gemm_n] of the output
   int N, H, W, C;            // input geometry (C = Cin)
   int Kc, R, S, stride, pad; // Kc = Cout
   int Ho, Wo;
@@ -91,6 +92,43 @@ __device__ __forceinline__ uint32_t virt2kb(const ConvParams& p, uint32_t v) {
 // Write NCOLS accumulator columns [nn0, nn0+NCOLS) of GEMM row m, 8 columns (one 16-byte bf16 vector) at a
 // time; gemm_n is a multiple of 8 in every mode.  FWD: +bias, ReLU, bf16.  DGRAD: bf16.  WGRAD: fp32 red.add
 // into the gradient arena.  Kept small on purpose: a tile runs this code once, so its size is fetch latency.
+// BatchNorm statistics in the conv epilogue: every thread holds one output row (NCOLS fp32 accumulators); a butterfly of
+// NCOLS-1 shuffles leaves lane l with the warp's column-l total (instead of 5 shuffles per column), then one red.add
+// per column per warp into sums[channel] / sums[gemm_n + channel].  Rows beyond gemm_m are exact zeros (zero-filled
+// operands, no bias), so they need no mask.
+template <int NCOLS>
+__device__ __forceinline__ void bn_stats_accumulate(const ConvParams& p, uint32_t nn0, const float* f, int lane) {
+  static_assert(NCOLS == 8 || NCOLS == 16 || NCOLS == 32 || NCOLS == 64 || NCOLS == 128, "column block");
+  constexpr int W = NCOLS < 32 ? NCOLS : 32;
+#pragma unroll
+  for (int c0 = 0; c0 < NCOLS; c0 += 32) {
+    float s[W], q[W];
+#pragma unroll
+    for (int i = 0; i < W; ++i) { s[i] = f[c0 + i]; q[i] = s[i] * s[i]; }
+#pragma unroll
+    for (int st = W / 2; st >= 1; st >>= 1) {
+      const bool up = (lane & st) != 0;
+#pragma unroll
+      for (int i = 0; i < st; ++i) {
+        const float ks = up ? s[i + st] : s[i], ss = up ? s[i] : s[i + st];
+        const float kq = up ? q[i + st] : q[i], sq = up ? q[i] : q[i + st];
+        s[i] = ks + __shfl_xor_sync(0xffffffffu, ss, st);
+        q[i] = kq + __shfl_xor_sync(0xffffffffu, sq, st);
+      }
+    }
+#pragma unroll
+    for (int st = W; st < 32; st <<= 1) {                     // narrow blocks: the lanes above W hold the other partials
+      s[0] += __shfl_xor_sync(0xffffffffu, s[0], st);
+      q[0] += __shfl_xor_sync(0xffffffffu, q[0], st);
+    }
+    const uint32_t ch = nn0 + c0 + (lane & (W - 1));
+    if (lane < W && ch < p.gemm_n) {
+      atomicAdd(p.bn_sums + ch, s[0]);
+      atomicAdd(p.bn_sums + p.gemm_n + ch, q[0]);
+    }
+  }
+}
+
 template <int MODE, int NCOLS>
 __device__ __forceinline__ void epilogue_store(const ConvParams& p, uint32_t m, uint32_t nn0, float* f) {
   if (m >= p.gemm_m) return;
@@ -409,6 +447,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
 #pragma unroll
             for (int q = 0; q < 32; ++q) f[q] = 0.f;
           }
+          if (MODE == MODE_FWD && p.bn_sums != nullptr) bn_stats_accumulate<32>(p, n0 + cb * 32, f, lane);
           epilogue_store<MODE, 32>(p, m, n0 + cb * 32, f);
         }
       }
@@ -470,6 +509,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
 #pragma unroll
         for (int q = 0; q < SLICE; ++q) f[q] += ld_dsmem_f32(base + (uint32_t)q * BM * 4u);
       }
+      if (MODE == MODE_FWD && p.bn_sums != nullptr) bn_stats_accumulate<SLICE>(p, n0 + rank * SLICE, f, lane);
       if (MODE != MODE_WGRAD || p.nvk > 0) epilogue_store<MODE, SLICE>(p, m, n0 + rank * SLICE, f);
     }
     STAMP(6, 0);
@@ -665,13 +705,14 @@ extern "C" int b200_conv_set_split_k(int enabled) {
   return 0;
 }
 
-extern "C" int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g,
-                             int relu, void* stream) {
+static int conv_fwd_impl(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g, int relu,
+                         float* bn_sums, void* stream) {
   ConvParams p;
   int rc = fill_common(p, g);
   if (rc) return rc;
   B200_REQUIRE(x && w && y, "null tensor");
-  p.x = (const __nv_bfloat16*)x; p.w = (const __nv_bfloat16*)w; p.out = y; p.bias = bias; p.relu = relu;
+  B200_REQUIRE(bn_sums == nullptr || (bias == nullptr && !relu), "BN statistics are taken of the raw conv output: no bias, no ReLU");
+  p.x = (const __nv_bfloat16*)x; p.w = (const __nv_bfloat16*)w; p.out = y; p.bias = bias; p.relu = relu; p.bn_sums = bn_sums;
   p.gemm_m = (uint32_t)p.N * p.Ho * p.Wo; p.gemm_n = p.Kc; p.gemm_k = (uint32_t)p.R * p.S * p.C;
   plan_k(p, p.C);
   const bool narrow = p.gemm_n <= 64;
@@ -687,6 +728,20 @@ extern "C" int b200_conv_fwd(const void* x, const void* w, const float* bias, vo
   p.a_tma = (plain && make_tmap_2d(&tmA, x, p.gemm_k, p.gemm_m, BM)) ? 1u : 0u;             // x as [M][C]
   return narrow ? launch<MODE_FWD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
                 : launch<MODE_FWD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
+}
+
+extern "C" int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g,
+                             int relu, void* stream) {
+  return conv_fwd_impl(x, w, bias, y, g, relu, nullptr, stream);
+}
+
+// Same convolution (no bias, no ReLU), and the epilogue also adds the per-channel sum and sum of squares of the fp32
+// output into bn_sums[0..Kc) / bn_sums[Kc..2Kc): the statistics pass of a following training-mode BatchNorm for free.
+// bn_sums must be zero on entry (b200_bn_finalize leaves it zero again).
+extern "C" int b200_conv_fwd_stats(const void* x, const void* w, void* y, const b200_conv_geom* g, float* bn_sums,
+                                   void* stream) {
+  B200_REQUIRE(bn_sums != nullptr, "null bn_sums");
+  return conv_fwd_impl(x, w, nullptr, y, g, 0, bn_sums, stream);
 }
 
 extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream) {
@@ -740,10 +795,13 @@ extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b
     if (live_n_tiles == 0) return 0;
   }
   const uint32_t tiles = ((p.gemm_m + BM - 1) / BM) * live_n_tiles;
-  // split the position reduction so the grid covers the machine ~2x (>= 2 k-blocks per CTA): the `zc` CTAs of a
-  // cluster reduce through DSMEM so only one red.add per element leaves the cluster; `zo` such clusters
-  // accumulate through the atomics.
-  uint32_t splits = (2u * (uint32_t)b200_num_sms() + tiles - 1) / tiles;
+  // Split the position reduction over about half the SMs (B200DDP_WGRAD_SM_PCT, default 60), >= 2 k-blocks per CTA.
+  // The kernel's cost is per-CTA latency, not math: clusters of 4 at 1 CTA/SM only fit ~32 at a time (GPCs of 18-20
+  // SMs), so a grid of 148+ CTAs runs in two or three waves (23-31 us on the resnet18 shapes) where 74 CTAs take
+  // one (~11 us) and leave SMs to the dgrad / BN kernels that run concurrently on the main stream.  The `zc` CTAs of a
+  // cluster reduce through DSMEM so only one red.add per element leaves the cluster; `zo` clusters meet in the atomics.
+  static const uint32_t sm_pct = []() { const char* e = getenv("B200DDP_WGRAD_SM_PCT"); const int v = e ? atoi(e) : 60; return (uint32_t)(v < 1 ? 1 : v); }();
+  uint32_t splits = ((uint32_t)b200_num_sms() * sm_pct / 100u) / tiles;
   if (max_splits > 0 && splits > (uint32_t)max_splits) splits = (uint32_t)max_splits;
   const uint32_t max_by_k = (kblocks + 1) / 2;
   if (splits > max_by_k) splits = max_by_k;

@@ -220,6 +220,11 @@ int b200_conv_set_split_k(int enabled);
 int b200_conv_set_profile_buffer(long long* dev_buf8);
 int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g, int relu,
                   void* stream);
+/* the same convolution without bias/ReLU whose epilogue also accumulates per-channel sum / sum of squares of the output
+   into bn_sums[2][Kc] (zero on entry): the statistics of a following training-mode BatchNorm; see b200_bn_finalize */
+int b200_conv_fwd_stats(const void* x, const void* w, void* y, const b200_conv_geom* g, float* bn_sums, void* stream);
+int b200_bn_finalize(float* sums, size_t rows, int C, const float* gamma, const float* beta, float eps, float momentum,
+                     float* stat, float* running_mean, float* running_var, void* stream);
 int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream);
 int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
                     void* stream);

@@ -393,3 +393,31 @@ def test_audio_and_text_models_native_paths_match_cpu():
     ref.emb_forward(er).sum().backward()
     gpu.emb_forward(eg).sum().backward()
     assert _rel(eg.grad, er.grad) < 1e-3
+
+
+def test_conv_epilogue_bn_stats_and_finalize_match_bn_stats_kernel():
+    """conv_fwd(bn_sums=) + bn_finalize == conv_fwd + bn_stats (the separate statistics pass), for a direct tile and a
+    cluster split-K shape; the sums are left zero."""
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    torch.manual_seed(4)
+    for (N, C, H, K, st) in [(64, 64, 8, 64, 1), (256, 128, 4, 128, 1), (64, 64, 8, 128, 2), (32, 16, 16, 24, 1)]:
+        x = _act(N, C, H, H, dev)
+        w = (torch.randn(K, 3, 3, C, device=dev) / (3 * C ** 0.5)).to(torch.bfloat16)
+        gam, bet = torch.rand(K, device=dev) + 0.5, torch.randn(K, device=dev)
+        rm1, rv1 = torch.zeros(K, device=dev), torch.ones(K, device=dev)
+        rm2, rv2 = torch.zeros(K, device=dev), torch.ones(K, device=dev)
+        y_ref = nv.conv_fwd(x, w, None, st, 1, False)
+        stat_ref = nv.bn_stats(y_ref, gam, bet, 1e-5, 0.1, rm1, rv1)
+        sums = torch.zeros(2 * K, device=dev)
+        y = nv.conv_fwd(x, w, None, st, 1, False, sums)
+        rows = y.numel() // K
+        stat = nv.bn_finalize(sums, rows, gam, bet, 1e-5, 0.1, rm2, rv2)
+        torch.cuda.synchronize()
+        assert torch.equal(y, y_ref)
+        assert float(sums.abs().max()) == 0.0
+        # the separate pass reads the bf16-rounded tensor, the epilogue the fp32 accumulators: equal up to that rounding
+        assert torch.allclose(stat[0], stat_ref[0], atol=3e-3), (N, C, H, K)
+        assert torch.allclose(stat[1], stat_ref[1], rtol=5e-3)
+        assert torch.allclose(stat[2], stat_ref[2], rtol=5e-3) and torch.allclose(stat[3], stat_ref[3], atol=2e-2)
+        assert torch.allclose(rm2, rm1, atol=1e-3) and torch.allclose(rv2, rv1, rtol=5e-3)
