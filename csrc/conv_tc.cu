@@ -44,8 +44,9 @@ namespace {
 constexpr int MODE_FWD = 0, MODE_DGRAD = 1, MODE_WGRAD = 2;
 constexpr int BM = 128;
 constexpr int BK = 64;                 // bf16 elements per k-block = one 128-byte swizzle row
-constexpr int STAGES = 6;
-constexpr int LAG = 4;                 // cp.async groups kept in flight behind the newest one
+// Operand ring depth ST (template parameter): 6 stages / 1 CTA per SM for the latency-bound small problems, 3 stages /
+// 2 CTAs per SM for grids of many tiles (one tile's load latency and epilogue hide behind the other CTA's MMAs).
+constexpr int lag_for(int st) { return st >= 6 ? 4 : 2; }   // cp.async groups kept in flight behind the newest one
 constexpr int PRODUCERS = 128;
 constexpr int THREADS = PRODUCERS + 32;
 long long* g_prof = nullptr;           // b200_conv_set_profile_buffer
@@ -73,14 +74,14 @@ struct ConvParams {
   FastDiv div_c, div_s, div_kc, div_wo, div_ho, div_w, div_h, div_cpt;
 };
 
-template <int MODE, int BN>
+template <int MODE, int BN, int ST = 6>
 struct Cfg {
   static constexpr bool A_MN = (MODE == MODE_WGRAD);
   static constexpr bool B_MN = (MODE != MODE_FWD);
   static constexpr int A_BYTES = BM * BK * 2;          // 16 KiB either way
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 2048 /*row info*/;
+  static constexpr int SMEM_BYTES = ST * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 2048 /*row info*/;
 };
 
 __device__ __forceinline__ uint32_t virt2kb(const ConvParams& p, uint32_t v) {
@@ -159,11 +160,12 @@ __device__ __forceinline__ void epilogue_store(const ConvParams& p, uint32_t m, 
   }
 }
 
-template <int MODE, int BN, int ZC>
-__global__ void __launch_bounds__(THREADS, 1)
+template <int MODE, int BN, int ZC, int ST>
+__global__ void __launch_bounds__(THREADS, (ST <= 3 ? 2 : 1))
 conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUtensorMap tmA,
                const __grid_constant__ CUtensorMap tmB) {
-  using C = Cfg<MODE, BN>;
+  using C = Cfg<MODE, BN, ST>;
+  constexpr int STAGES = ST, LAG = lag_for(ST);
   pdl_trigger();                  // the next kernel of the stream may be scheduled now; it waits for us in its own pdl_wait()
   const uint32_t m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   if (MODE == MODE_WGRAD && p.cpt != 0) {
@@ -526,12 +528,15 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
 }
 
 // ------------------------------------------------------------------------------------------------
-template <int MODE, int BN, int ZC>
+// tiles per SM from which the 3-stage / 2-CTAs-per-SM variant is used (B200DDP_TWO_CTA_TILES; 0 = never)
+static const uint32_t g_two_cta_tiles = []() { const char* e = getenv("B200DDP_TWO_CTA_TILES"); const int v = e ? atoi(e) : 2; return (uint32_t)(v < 1 ? 1000000 : v); }();
+
+template <int MODE, int BN, int ZC, int ST = 6>
 int launch_zc(const ConvParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, dim3 grid, cudaStream_t s) {
-  using C = Cfg<MODE, BN>;
+  using C = Cfg<MODE, BN, ST>;
   static bool attr_set = false;
   if (!attr_set) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<MODE, BN, ZC>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<MODE, BN, ZC, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_set = true;
   }
   cudaLaunchConfig_t cfg;
@@ -556,14 +561,17 @@ int launch_zc(const ConvParams& p, const CUtensorMap& tmA, const CUtensorMap& tm
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<MODE, BN, ZC>, p, tmA, tmB));
+  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<MODE, BN, ZC, ST>, p, tmA, tmB));
   return 0;
 }
 
 template <int MODE, int BN>
 int launch(const ConvParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, dim3 grid, uint32_t zc, cudaStream_t s) {
   switch (zc) {
-    case 1: return launch_zc<MODE, BN, 1>(p, tmA, tmB, grid, s);
+    case 1:
+      // many tiles per SM: two smaller CTAs per SM overlap each other's load latency and epilogue
+      if ((size_t)grid.x * grid.y >= (size_t)g_two_cta_tiles * b200_num_sms()) return launch_zc<MODE, BN, 1, 3>(p, tmA, tmB, grid, s);
+      return launch_zc<MODE, BN, 1>(p, tmA, tmB, grid, s);
     case 2: return launch_zc<MODE, BN, 2>(p, tmA, tmB, grid, s);
     case 4: return launch_zc<MODE, BN, 4>(p, tmA, tmB, grid, s);
     case 8: return launch_zc<MODE, BN, 8>(p, tmA, tmB, grid, s);

@@ -45,6 +45,9 @@ CONV_CASES = [
     (8, 512, 2, 2, 512, 3, 1, 1),     # split-K with many splits
     (256, 512, 1, 1, 512, 3, 1, 1),   # 8 of 9 taps dead: tap skipping + split-K
     (64, 128, 4, 4, 256, 1, 2, 0),    # 1x1 stride 2: dgrad tiles with no live tap
+    (16, 64, 56, 56, 64, 3, 1, 1),    # 392 tiles: the 3-stage, two-CTAs-per-SM variant (cp.async gathers)
+    (16, 256, 56, 56, 64, 1, 1, 0),   # same variant with both operands on TMA (1x1)
+    (24, 64, 56, 56, 256, 1, 1, 0),   # ... and 128-wide N tiles
 ]
 
 
