@@ -52,7 +52,7 @@ class Conv2d(nn.Conv2d):
             if rows > BF.nv.BN_SMALL_ROWS:      # small tensors: BN's single-launch kernel is cheaper than finalize + apply
                 kp = BF.ceil8(self.out_channels)
                 if self._bn_sums is None or self._bn_sums.device != x.device:
-                    self._bn_sums = torch.zeros(2 * kp, dtype=torch.float32, device=x.device)   # zero at rest
+                    self._bn_sums = torch.zeros(2 * kp + 1, dtype=torch.float32, device=x.device)   # sums + ticket, zero at rest
                 y = BF.conv2d(x, self.weight, None, self.stride[0], self.padding[0], False, self._bn_sums)
                 y._b200_bn_sums = self._bn_sums
                 return y

@@ -91,7 +91,7 @@ def conv_fwd(x: torch.Tensor, w_krsc: torch.Tensor, bias: Optional[torch.Tensor]
     y = empty_act(N, K, Ho, Wo, x.device)
     g = _geom(N, H, W, C, K, R, S, stride, pad)
     if bn_sums is not None:
-        assert bias is None and not relu and bn_sums.numel() == 2 * K and bn_sums.dtype == torch.float32
+        assert bias is None and not relu and bn_sums.numel() >= 2 * K and bn_sums.dtype == torch.float32
         L.check(L.lib().b200_conv_fwd_stats(L.ptr(x), L.ptr(w_krsc), L.ptr(y), byref(g), L.ptr(bn_sums), L.stream_ptr()),
                 "conv_fwd_stats")
         return y
@@ -180,6 +180,18 @@ def bn_finalize(sums: torch.Tensor, rows: int, gamma, beta, eps: float, momentum
                                      c_float(momentum), L.ptr(stat), L.ptr(running_mean), L.ptr(running_var), L.stream_ptr()),
             "bn_finalize")
     return stat
+
+
+def bn_apply_sums(x, residual, sums, gamma, beta, eps: float, momentum: float, running_mean, running_var, relu: bool):
+    """``bn_finalize`` + ``bn_apply`` in one launch; ``sums`` holds 2C floats + 1 ticket word.  Returns (y, stat)."""
+    rows, C = _rows_c(x)
+    assert sums.numel() >= 2 * C + 1
+    stat = torch.empty((4, C), dtype=torch.float32, device=x.device)
+    y = torch.empty_like(x)
+    L.check(L.lib().b200_bn_apply_sums(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(sums), L.ptr(gamma),
+                                       L.ptr(beta), c_float(eps), c_float(momentum), L.ptr(stat), L.ptr(running_mean),
+                                       L.ptr(running_var), c_int(int(relu)), L.stream_ptr()), "bn_apply_sums")
+    return y, stat
 
 
 def bn_eval_prep(gamma, beta, running_mean, running_var, eps: float) -> torch.Tensor:

@@ -224,6 +224,74 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
   }
 }
 
+// bn_apply fed by the per-channel sums of the conv epilogue (b200_conv_fwd_stats): every CTA derives scale/shift for its
+// channel group from the sums, CTA row 0 also writes `stat` (for the backward pass) and the running statistics, and the
+// last CTA to have read the sums (ticket in sums[2C]) zeroes them for the next forward.  One launch, no finalize kernel.
+template <bool kRelu, bool kRes>
+__global__ void __launch_bounds__(kThreads)
+bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
+                     __nv_bfloat16* __restrict__ y, size_t rows, int C, float* __restrict__ sums,
+                     const float* __restrict__ gamma, const float* __restrict__ beta, float eps, float momentum,
+                     float* __restrict__ stat, float* __restrict__ running_mean, float* __restrict__ running_var) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ bool last;
+  const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
+  const int c = blockIdx.y * kGroup + v * 8;
+  const bool live = c < C;
+  float sc[8], sh[8];
+  if (live) {
+    const float inv_n = 1.f / (float)rows;
+    const bool writer = blockIdx.x == 0 && rl == 0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float mean = __ldcg(sums + c + k) * inv_n;
+      const float var = fmaxf(__ldcg(sums + C + c + k) * inv_n - mean * mean, 0.f);
+      const float rstd = rsqrtf(var + eps);
+      sc[k] = gamma[c + k] * rstd;
+      sh[k] = beta[c + k] - mean * sc[k];
+      if (writer) {
+        stat[c + k] = mean;
+        stat[C + c + k] = rstd;
+        stat[2 * C + c + k] = sc[k];
+        stat[3 * C + c + k] = sh[k];
+        if (running_mean != nullptr) {
+          const float unbiased = rows > 1 ? var * (float)rows / (float)(rows - 1) : var;
+          running_mean[c + k] = (1.f - momentum) * running_mean[c + k] + momentum * mean;
+          running_var[c + k] = (1.f - momentum) * running_var[c + k] + momentum * unbiased;
+        }
+      }
+    }
+  }
+  __syncthreads();                                            // every thread of this CTA has read its sums
+  if (threadIdx.x == 0) {
+    unsigned* counter = reinterpret_cast<unsigned*>(sums + 2 * C);
+    __threadfence();
+    const unsigned ticket = atomicAdd(counter, 1u);
+    last = ticket == gridDim.x * gridDim.y - 1;
+    if (last) *counter = 0u;
+  }
+  __syncthreads();
+  if (last) {
+    for (int i = threadIdx.x; i < 2 * C; i += kThreads) sums[i] = 0.f;
+  }
+  if (!live) return;
+  for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
+    float f[8];
+    bf16x8_to_float(ld_vec(x + r * C + c), f);
+    float rr[8];
+    if (kRes) bf16x8_to_float(ld_vec(res + r * C + c), rr);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float o = fmaf(f[k], sc[k], sh[k]);
+      if (kRes) o += rr[k];
+      if (kRelu) o = fmaxf(o, 0.f);
+      f[k] = o;
+    }
+    st_vec(y + r * C + c, float_to_bf16x8(f));
+  }
+}
+
 template <bool kRelu>
 __global__ void __launch_bounds__(kThreads)
 bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
@@ -710,6 +778,27 @@ extern "C" int b200_bn_finalize(float* sums, size_t rows, int C, const float* ga
   B200_REQUIRE(sums && gamma && beta && stat && rows > 0 && C > 0, "bad bn_finalize argument");
   b200_launch(bn_finalize_kernel, dim3((C + 127) / 128), dim3(128), 0, (cudaStream_t)stream, sums, rows, C, gamma, beta, eps,
               momentum, stat, running_mean, running_var);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// BN(+residual)(+ReLU) forward in ONE launch from the conv epilogue's sums: sums[0..C) sum, [C..2C) sum of squares,
+// sums[2C] a ticket word; all zero on entry and zero again afterwards.  Also writes stat[4][C] and the running statistics.
+extern "C" int b200_bn_apply_sums(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C, float* sums,
+                                  const float* gamma, const float* beta, float eps, float momentum, float* stat,
+                                  float* running_mean, float* running_var, int relu, void* stream) {
+  B200_REQUIRE(x_bf16 && y_bf16 && sums && gamma && beta && stat, "null argument");
+  B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
+  dim3 g = bn_grid(rows, C, 8);
+  cudaStream_t s = (cudaStream_t)stream;
+  const __nv_bfloat16 *x = (const __nv_bfloat16*)x_bf16, *r = (const __nv_bfloat16*)residual_bf16;
+  __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
+#define B200_BNAS(R, S) b200_launch(bn_apply_sums_kernel<R, S>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, sums, gamma, beta, eps, momentum, stat, running_mean, running_var)
+  if (relu && r) B200_BNAS(true, true);
+  else if (relu) B200_BNAS(true, false);
+  else if (r) B200_BNAS(false, true);
+  else B200_BNAS(false, false);
+#undef B200_BNAS
   B200_CHECK_LAUNCH();
   return 0;
 }

@@ -225,6 +225,10 @@ int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, cons
 int b200_conv_fwd_stats(const void* x, const void* w, void* y, const b200_conv_geom* g, float* bn_sums, void* stream);
 int b200_bn_finalize(float* sums, size_t rows, int C, const float* gamma, const float* beta, float eps, float momentum,
                      float* stat, float* running_mean, float* running_var, void* stream);
+/* bn_finalize + bn_apply in one launch; sums has 2C floats + one ticket word, zero on entry and on exit */
+int b200_bn_apply_sums(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C, float* sums,
+                       const float* gamma, const float* beta, float eps, float momentum, float* stat,
+                       float* running_mean, float* running_var, int relu, void* stream);
 int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream);
 int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
                     void* stream);

@@ -424,3 +424,14 @@ def test_conv_epilogue_bn_stats_and_finalize_match_bn_stats_kernel():
         assert torch.allclose(stat[1], stat_ref[1], rtol=5e-3)
         assert torch.allclose(stat[2], stat_ref[2], rtol=5e-3) and torch.allclose(stat[3], stat_ref[3], atol=2e-2)
         assert torch.allclose(rm2, rm1, atol=1e-3) and torch.allclose(rv2, rv1, rtol=5e-3)
+        # one-launch variant: finalize folded into bn_apply (ticket word after the sums)
+        sums3 = torch.zeros(2 * K + 1, device=dev)
+        rm3, rv3 = torch.zeros(K, device=dev), torch.ones(K, device=dev)
+        res = torch.randn_like(y)
+        y3 = nv.conv_fwd(x, w, None, st, 1, False, sums3)
+        out3, stat3 = nv.bn_apply_sums(y3, res, sums3, gam, bet, 1e-5, 0.1, rm3, rv3, True)
+        out_ref = nv.bn_apply(y_ref, res, stat, True)
+        torch.cuda.synchronize()
+        assert float(sums3.abs().max()) == 0.0
+        assert torch.allclose(stat3, stat, rtol=1e-4, atol=1e-5) and torch.allclose(rm3, rm2, atol=1e-6) and torch.allclose(rv3, rv2, rtol=1e-5)
+        assert torch.allclose(out3.float(), out_ref.float(), atol=2e-2, rtol=2e-2)
