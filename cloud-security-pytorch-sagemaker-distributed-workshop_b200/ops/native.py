@@ -100,12 +100,19 @@ def conv_fwd(x: torch.Tensor, w_krsc: torch.Tensor, bias: Optional[torch.Tensor]
     return y
 
 
-def conv_dgrad(dy: torch.Tensor, w_krsc: torch.Tensor, x_shape, stride: int, pad: int) -> torch.Tensor:
+def conv_dgrad(dy: torch.Tensor, w_krsc: torch.Tensor, x_shape, stride: int, pad: int,
+               residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """dx = dgrad(dy, w) (+ residual, a channels-last bf16 tensor of dx's shape, added in the epilogue)."""
     N, C, H, W = x_shape
     K, R, S, _ = w_krsc.shape
     assert _cl_ok(dy)
     dx = empty_act(N, C, H, W, dy.device)
     g = _geom(N, H, W, C, K, R, S, stride, pad)
+    if residual is not None:
+        assert tuple(residual.shape) == (N, C, H, W) and _cl_ok(residual) and residual.dtype == torch.bfloat16
+        L.check(L.lib().b200_conv_dgrad_add(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.ptr(residual), L.stream_ptr()),
+                "conv_dgrad_add")
+        return dx
     L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.stream_ptr()), "conv_dgrad")
     return dx
 

@@ -58,6 +58,7 @@ struct ConvParams {
   const __nv_bfloat16* dy;   // output-side tensor (DGRAD/WGRAD)
   void* out;                 // FWD: y bf16 [M][Cout]; DGRAD: dx bf16 [M][Cin]; WGRAD: dw fp32 [Cout][R*S*Cin]
   const float* bias;         // FWD only, may be null
+  const __nv_bfloat16* residual;   // DGRAD only, may be null: added to the output (the other gradient of a forked tensor)
   float* bn_sums;            // FWD only, may be null: per-channel sum [gemm_n] and sum of squares [gemm_n] of the output
   int N, H, W, C;            // input geometry (C = Cin)
   int Kc, R, S, stride, pad; // Kc = Cout
@@ -90,9 +91,6 @@ __device__ __forceinline__ uint32_t virt2kb(const ConvParams& p, uint32_t v) {
   return (uint32_t)p.tap_list[q] * p.cpt + (v - q * p.cpt);
 }
 
-// Write NCOLS accumulator columns [nn0, nn0+NCOLS) of GEMM row m, 8 columns (one 16-byte bf16 vector) at a
-// time; gemm_n is a multiple of 8 in every mode.  FWD: +bias, ReLU, bf16.  DGRAD: bf16.  WGRAD: fp32 red.add
-// into the gradient arena.  Kept small on purpose: a tile runs this code once, so its size is fetch latency.
 // BatchNorm statistics in the conv epilogue: every thread holds one output row (NCOLS fp32 accumulators); a butterfly of
 // NCOLS-1 shuffles leaves lane l with the warp's column-l total (instead of 5 shuffles per column), then one red.add
 // per column per warp into sums[channel] / sums[gemm_n + channel].  Rows beyond gemm_m are exact zeros (zero-filled
@@ -130,9 +128,18 @@ __device__ __forceinline__ void bn_stats_accumulate(const ConvParams& p, uint32_
   }
 }
 
+// Write NCOLS accumulator columns [nn0, nn0+NCOLS) of GEMM row m, 8 columns (one 16-byte bf16 vector) at a
+// time; gemm_n is a multiple of 8 in every mode.  FWD: +bias, ReLU, bf16.  DGRAD: (+residual) bf16.  WGRAD: fp32 red.add
+// into the gradient arena.  Kept small on purpose: a tile runs this code once, so its size is fetch latency.
 template <int MODE, int NCOLS>
 __device__ __forceinline__ void epilogue_store(const ConvParams& p, uint32_t m, uint32_t nn0, float* f) {
   if (m >= p.gemm_m) return;
+  bf16x8 resv[NCOLS / 8];
+  if (MODE == MODE_DGRAD && p.residual != nullptr) {        // all of this row's residual vectors in flight at once
+#pragma unroll
+    for (int q = 0; q < NCOLS / 8; ++q)
+      if (nn0 + 8 * q < p.gemm_n) resv[q] = *reinterpret_cast<const bf16x8*>(p.residual + (size_t)m * p.gemm_n + nn0 + 8 * q);
+  }
 #pragma unroll
   for (int q = 0; q < NCOLS / 8; ++q) {
     const uint32_t nn = nn0 + 8 * q;
@@ -154,6 +161,12 @@ __device__ __forceinline__ void epilogue_store(const ConvParams& p, uint32_t m, 
 #pragma unroll
           for (int k = 0; k < 8; ++k) v[k] = fmaxf(v[k], 0.f);
         }
+      }
+      if (MODE == MODE_DGRAD && p.residual != nullptr) {
+        float r[8];
+        bf16x8_to_float(resv[q], r);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) v[k] += r[k];
       }
       *reinterpret_cast<bf16x8*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.gemm_n + nn) = float_to_bf16x8(v);
     }
@@ -752,13 +765,14 @@ extern "C" int b200_conv_fwd_stats(const void* x, const void* w, void* y, const 
   return conv_fwd_impl(x, w, nullptr, y, g, 0, bn_sums, stream);
 }
 
-extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream) {
+static int conv_dgrad_impl(const void* dy, const void* w, void* dx, const b200_conv_geom* g, const void* residual,
+                           void* stream) {
   ConvParams p;
   int rc = fill_common(p, g);
   if (rc) return rc;
   B200_REQUIRE(dy && w && dx, "null tensor");
   B200_REQUIRE(p.stride <= 2, "dgrad supports stride 1 and 2");
-  p.dy = (const __nv_bfloat16*)dy; p.w = (const __nv_bfloat16*)w; p.out = dx;
+  p.dy = (const __nv_bfloat16*)dy; p.w = (const __nv_bfloat16*)w; p.out = dx; p.residual = (const __nv_bfloat16*)residual;
   p.gemm_m = (uint32_t)p.N * p.H * p.W; p.gemm_n = p.C; p.gemm_k = (uint32_t)p.R * p.S * p.Kc;
   plan_k(p, p.Kc);
   const bool narrow = p.gemm_n <= 64;
@@ -773,6 +787,18 @@ extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b2
   p.a_tma = (plain && make_tmap_2d(&tmA, dy, p.gemm_k, p.gemm_m, BM)) ? 1u : 0u;            // dy as [M][Cout]
   return narrow ? launch<MODE_DGRAD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
                 : launch<MODE_DGRAD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
+}
+
+extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream) {
+  return conv_dgrad_impl(dy, w, dx, g, nullptr, stream);
+}
+
+// dx = dgrad(dy, w) + residual (bf16, same shape as dx): when the conv's input also feeds another branch (a ResNet skip
+// connection), that branch's gradient is added in the epilogue instead of by a separate elementwise kernel.
+extern "C" int b200_conv_dgrad_add(const void* dy, const void* w, void* dx, const b200_conv_geom* g, const void* residual,
+                                   void* stream) {
+  B200_REQUIRE(residual != nullptr, "null residual");
+  return conv_dgrad_impl(dy, w, dx, g, residual, stream);
 }
 
 extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,

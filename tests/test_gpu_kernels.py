@@ -435,3 +435,37 @@ def test_conv_epilogue_bn_stats_and_finalize_match_bn_stats_kernel():
         assert float(sums3.abs().max()) == 0.0
         assert torch.allclose(stat3, stat, rtol=1e-4, atol=1e-5) and torch.allclose(rm3, rm2, atol=1e-6) and torch.allclose(rv3, rv2, rtol=1e-5)
         assert torch.allclose(out3.float(), out_ref.float(), atol=2e-2, rtol=2e-2)
+
+
+def test_conv_dgrad_residual_epilogue_and_grad_mailbox():
+    """b200_conv_dgrad_add == dgrad + residual; a forked activation's two gradients meet in that epilogue (no autograd add)
+    and equal what plain autograd accumulation gives."""
+    from b200ddp import nn as bnn
+    from b200ddp.ops import functional as BF, native as nv
+    dev = _dev()
+    torch.manual_seed(6)
+    for (N, C, H, K, R, st, pad) in [(8, 64, 8, 64, 3, 1, 1), (8, 64, 8, 128, 1, 2, 0), (4, 128, 4, 128, 3, 2, 1)]:
+        Ho = (H + 2 * pad - R) // st + 1
+        dy = _act(N, K, Ho, Ho, dev)
+        w = (torch.randn(K, R, R, C, device=dev) / (R * C ** 0.5)).to(torch.bfloat16)
+        res = _act(N, C, H, H, dev)
+        plain = nv.conv_dgrad(dy, w, (N, C, H, H), st, pad)
+        fused = nv.conv_dgrad(dy, w, (N, C, H, H), st, pad, residual=res)
+        ref = (plain.float() + res.float()).to(torch.bfloat16)
+        assert (fused.float() - ref.float()).abs().max() <= 2e-2 * max(1.0, float(ref.float().abs().max()))
+    # block-level: y = relu(bn(conv(x)) + x) with the mailbox on and off
+    grads = {}
+    for on in (True, False):
+        BF._FUSE_SKIP_GRAD[0] = on
+        torch.manual_seed(7)
+        conv = bnn.Conv2d(64, 64, 3, padding=1, bias=False).to(dev)
+        bn = bnn.BatchNorm2d(64, relu=True).to(dev)
+        pre = bnn.Conv2d(64, 64, 1, bias=False).to(dev)
+        x0 = _act(16, 64, 8, 8, dev).requires_grad_(True)
+        x = BF.fork(pre(x0))
+        out = bn(conv(x), x)
+        out.float().square().mean().backward()
+        grads[on] = (x0.grad.clone(), pre.weight.grad.clone(), conv.weight.grad.clone())
+    BF._FUSE_SKIP_GRAD[0] = False
+    for a, b in zip(grads[True], grads[False]):
+        assert _rel(a, b) < 1e-2
