@@ -310,7 +310,7 @@ class _BatchNormFn(torch.autograd.Function):
         dy = nv.to_cl(dy) if dy.dim() == 4 else dy.contiguous()
         gs, bs = getattr(gamma, "_b200_sink", None), getattr(beta, "_b200_sink", None)
         C = gamma.numel()
-        small = (x.numel() // x.shape[1]) <= nv.BN_SMALL_ROWS
+        small = (x.numel() // x.shape[1]) <= max(nv.BN_SMALL_ROWS, nv.BN_BWD_FUSED_ROWS)      # one launch (CTA or cluster kernel)
         if gs is not None and bs is not None:
             # the arena is zeroed by the optimizer, so beta_accum=1 both overwrites and accumulates correctly
             if small:

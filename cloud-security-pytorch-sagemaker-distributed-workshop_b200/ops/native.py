@@ -221,6 +221,11 @@ def bn_apply(x: torch.Tensor, residual: Optional[torch.Tensor], stat: torch.Tens
 # wins while the per-thread row loop is short: measured on B200, 1024 rows (resnet18 layer3 at batch 256) is already
 # slower than the two multi-CTA launches.  B200DDP_BN_FUSED_ROWS overrides.
 BN_SMALL_ROWS = int(__import__("os").environ.get("B200DDP_BN_FUSED_ROWS", "256"))
+# The backward pass has a second one-launch kernel above that size: a thread-block cluster per 8 channels that keeps its
+# slice of dy / x / y in registers (one pass, DSMEM reduction).  It accepts up to 16384 rows (b200_bn_bwd_fused_max_rows())
+# but only wins up to ~2048: measured on resnet18, per-GPU batch 32 (rows 2048/512/128/32): 0.805 -> 0.715 ms per step;
+# batch 256 with a limit of 1024 / 4096 / 16384 rows: 1.072 / 1.096 / 1.156 ms (two-kernel path everywhere: 1.101).
+BN_BWD_FUSED_ROWS = int(__import__("os").environ.get("B200DDP_BN_BWD_FUSED_ROWS", "2048"))
 
 
 def bn_fwd_fused(x, residual, gamma, beta, eps, momentum, running_mean, running_var, relu: bool):

@@ -10,6 +10,7 @@
 // finalises (mean/rstd/scale/shift + running statistics, or dgamma/dbeta).  No atomics on data, no
 // memset, CUDA-graph replayable.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -406,6 +407,139 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
 // (forward) and reduce + apply (backward) are ONE launch each; the second pass over the rows hits L2.
 constexpr size_t kSmallRows = 2048;
 
+// ---- mid-size BN backward in ONE launch: a thread-block cluster per group of 8 channels ---------------------------
+// Each CTA of the cluster takes a slice of the rows, <= kClRows rows per thread, and keeps what it loaded (dy, x, y: 16 bytes
+// per row each) in registers.  The 16 per-channel sums go warp -> CTA -> cluster (distributed shared memory), after which
+// every CTA applies dx = gamma*rstd*(dy - mean(dy) - xhat*mean(dy*xhat)) to its registers and stores.  One pass over the
+// tensors and one launch instead of the reduce + apply pair (two passes, two launches, a grid-wide ticket).
+constexpr int kClRows = 8;
+constexpr int kClMaxCluster = 8;
+
+__device__ __forceinline__ uint32_t cl_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t cl_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ float cl_ld_peer(const float* local, uint32_t cta) {
+  uint32_t a;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(a) : "r"(cl_smem_u32(local)), "r"(cta));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(a) : "memory");
+  return v;
+}
+
+template <bool kRelu, bool kRes>
+__global__ void __launch_bounds__(kThreads)
+bn_bwd_cluster_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                      const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx,
+                      __nv_bfloat16* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
+                      float* __restrict__ dgamma, float* __restrict__ dbeta, float beta_accum, int rows_per_cta, int zc) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ float wsum[kThreads / 32][16];
+  __shared__ float tot_s[16];                                 // this CTA's totals, read by its peers
+  __shared__ float fin[16];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const uint32_t rank = cl_rank();
+  const int c = blockIdx.y * 8;
+  const size_t r0 = (size_t)rank * rows_per_cta;
+  const size_t r1 = r0 + rows_per_cta < rows ? r0 + rows_per_cta : rows;
+  float mean[8], rstd[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    mean[k] = stat[c + k];
+    rstd[k] = stat[C + c + k];
+  }
+  bf16x8 gv[kClRows], xv[kClRows], yv[kClRows];
+#pragma unroll
+  for (int i = 0; i < kClRows; ++i) {                         // everything this thread will ever read, in flight at once
+    const size_t r = r0 + tid + (size_t)i * kThreads;
+    if (r < r1) {
+      gv[i] = ld_vec(dy + r * C + c);
+      xv[i] = ld_vec(x + r * C + c);
+      if (kRelu) yv[i] = ld_vec(y + r * C + c);
+    }
+  }
+  float s[8], q[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[k] = q[k] = 0.f;
+#pragma unroll
+  for (int i = 0; i < kClRows; ++i) {
+    const size_t r = r0 + tid + (size_t)i * kThreads;
+    if (r < r1) {
+      float g[8], xf[8], yf[8];
+      bf16x8_to_float(gv[i], g);
+      bf16x8_to_float(xv[i], xf);
+      if (kRelu) bf16x8_to_float(yv[i], yf);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float gg = (kRelu && !(yf[k] > 0.f)) ? 0.f : g[k];
+        s[k] += gg;
+        q[k] = fmaf(gg, (xf[k] - mean[k]) * rstd[k], q[k]);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    s[k] = warp_sum(s[k]);
+    q[k] = warp_sum(q[k]);
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { wsum[warp][k] = s[k]; wsum[warp][8 + k] = q[k]; }
+  }
+  __syncthreads();
+  if (tid < 16) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < kThreads / 32; ++w) t += wsum[w][tid];
+    tot_s[tid] = t;
+  }
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+  if (tid < 16) {
+    float t = 0.f;
+    for (int z = 0; z < zc; ++z) t += cl_ld_peer(&tot_s[tid], (uint32_t)z);      // same order in every CTA: identical totals
+    fin[tid] = t;
+    if (rank == 0) {
+      float* dst = tid < 8 ? dbeta : dgamma;
+      const int ch = c + (tid & 7);
+      if (dst != nullptr) dst[ch] = beta_accum != 0.f ? fmaf(beta_accum, dst[ch], t) : t;
+    }
+  }
+  __syncthreads();
+  const float inv_n = 1.f / (float)rows;
+  float a[8], m1[8], m2[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    a[k] = stat[2 * C + c + k];
+    m1[k] = fin[k] * inv_n;
+    m2[k] = fin[8 + k] * inv_n;
+  }
+#pragma unroll
+  for (int i = 0; i < kClRows; ++i) {
+    const size_t r = r0 + tid + (size_t)i * kThreads;
+    if (r < r1) {
+      float g[8], xf[8], yf[8];
+      bf16x8_to_float(gv[i], g);
+      bf16x8_to_float(xv[i], xf);
+      if (kRelu) bf16x8_to_float(yv[i], yf);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float gg = (kRelu && !(yf[k] > 0.f)) ? 0.f : g[k];
+        g[k] = gg;
+        xf[k] = a[k] * (gg - m1[k] - (xf[k] - mean[k]) * rstd[k] * m2[k]);
+      }
+      st_vec(dx + r * C + c, float_to_bf16x8(xf));
+      if (kRes) st_vec(dres + r * C + c, float_to_bf16x8(g));
+    }
+  }
+  // nobody leaves while a peer may still be reading its tot_s
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
+}
+
 template <bool kRelu, bool kRes>
 __global__ void __launch_bounds__(kThreads)
 bn_fwd_small_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
@@ -730,6 +864,11 @@ extern "C" int b200_bn_stats_noalloc(const void* x_bf16, size_t rows, int C, con
 
 extern "C" size_t b200_bn_small_rows(void) { return kSmallRows; }
 
+// rows above which b200_bn_bwd_fused switches from the one-CTA-per-64-channels kernel to the cluster kernel
+// (B200DDP_BN_CLUSTER_MIN_ROWS, default 256); the cluster kernel takes up to 8 rows x 256 threads x 8 CTAs.
+static const size_t g_bn_cluster_min_rows = []() { const char* e = getenv("B200DDP_BN_CLUSTER_MIN_ROWS"); return (size_t)(e ? atoll(e) : 256); }();
+extern "C" size_t b200_bn_bwd_fused_max_rows(void) { return (size_t)kClRows * kThreads * kClMaxCluster; }
+
 extern "C" int b200_bn_fwd_fused(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C,
                                  const float* gamma, const float* beta, float eps, float momentum, float* stat,
                                  float* running_mean, float* running_var, int relu, void* stream) {
@@ -756,11 +895,40 @@ extern "C" int b200_bn_bwd_fused(const void* dy_bf16, const void* x_bf16, const 
   B200_REQUIRE(dy_bf16 && x_bf16 && dx_bf16 && stat, "null argument");
   B200_REQUIRE(!relu || y_bf16, "relu mask needs y");
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
-  B200_REQUIRE(rows <= kSmallRows, "fused BN backward handles at most b200_bn_small_rows() rows");
-  dim3 g(1, (C + kGroup - 1) / kGroup, 1);
+  B200_REQUIRE(rows <= b200_bn_bwd_fused_max_rows(), "fused BN backward handles at most b200_bn_bwd_fused_max_rows() rows");
   cudaStream_t s = (cudaStream_t)stream;
   const __nv_bfloat16 *dy = (const __nv_bfloat16*)dy_bf16, *x = (const __nv_bfloat16*)x_bf16, *y = (const __nv_bfloat16*)y_bf16;
   __nv_bfloat16 *dx = (__nv_bfloat16*)dx_bf16, *dr = (__nv_bfloat16*)dres_bf16;
+  if (rows > g_bn_cluster_min_rows || rows > kSmallRows) {
+    // cluster kernel: 8 channels per cluster; grow the cluster until ~96 CTAs are in flight or a thread has one row
+    const int per_cta_max = kClRows * kThreads;
+    int zc = 1;
+    while ((size_t)zc * per_cta_max < rows) zc *= 2;
+    while (zc < kClMaxCluster && (C / 8) * zc < 96 && rows / (size_t)(2 * zc) >= (size_t)kThreads / 2) zc *= 2;
+    const int rows_per_cta = (int)((rows + zc - 1) / zc);
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(zc, C / 8, 1);
+    cfg.blockDim = dim3(kThreads, 1, 1);
+    cfg.stream = s;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = zc;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = b200_pdl_enabled() ? 2 : 1;
+#define B200_BNC(R, S) B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, bn_bwd_cluster_kernel<R, S>, dy, x, y, dx, dr, rows, C, stat, dgamma, dbeta, beta_accum, rows_per_cta, zc))
+    if (relu && dr) B200_BNC(true, true);
+    else if (relu) B200_BNC(true, false);
+    else if (dr) B200_BNC(false, true);
+    else B200_BNC(false, false);
+#undef B200_BNC
+    return 0;
+  }
+  dim3 g(1, (C + kGroup - 1) / kGroup, 1);
 #define B200_BNB(R, S) b200_launch(bn_bwd_small_kernel<R, S>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, dgamma, dbeta, beta_accum)
   if (relu && dr) B200_BNB(true, true);
   else if (relu) B200_BNB(true, false);

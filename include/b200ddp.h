@@ -159,6 +159,8 @@ int b200_bn_bwd_apply(const void* dy_bf16, const void* x_bf16, const void* y_bf1
                       void* stream);
 /* One-launch variants for small tensors (rows <= b200_bn_small_rows()): statistics+apply, reduce+apply. */
 size_t b200_bn_small_rows(void);
+/* b200_bn_bwd_fused: one CTA per 64 channels up to B200DDP_BN_CLUSTER_MIN_ROWS rows, a cluster per 8 channels above */
+size_t b200_bn_bwd_fused_max_rows(void);
 int b200_bn_fwd_fused(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C,
                       const float* gamma, const float* beta, float eps, float momentum, float* stat,
                       float* running_mean, float* running_var, int relu, void* stream);

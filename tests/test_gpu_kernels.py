@@ -469,3 +469,28 @@ def test_conv_dgrad_residual_epilogue_and_grad_mailbox():
     BF._FUSE_SKIP_GRAD[0] = False
     for a, b in zip(grads[True], grads[False]):
         assert _rel(a, b) < 1e-2
+
+
+@pytest.mark.parametrize("shape,relu,res", [((256, 64, 8, 8), True, True), ((256, 128, 4, 4), True, False), ((256, 256, 2, 2), False, True),
+                                             ((32, 64, 8, 8), True, True), ((37, 72, 5, 3), True, True), ((250, 64, 8, 8), True, False)])
+def test_batchnorm_backward_cluster_kernel_matches_two_pass(shape, relu, res):
+    """Mid-size tensors: the one-launch cluster kernel (registers + DSMEM reduction) == the reduce/apply pair, also for row
+    counts that do not divide evenly over the cluster and for an accumulating dgamma/dbeta."""
+    from b200ddp.ops import native as nv
+    dev = _dev()
+    torch.manual_seed(8)
+    N, C, H, W = shape
+    x = _act(N, C, H, W, dev, 2.0)
+    r = _act(N, C, H, W, dev) if res else None
+    gamma, beta = torch.rand(C, device=dev) + 0.5, torch.randn(C, device=dev)
+    stat = nv.bn_stats(x, gamma, beta, 1e-5, 0.1, None, None)
+    y = nv.bn_apply(x, r, stat, relu)
+    dy = _act(N, C, H, W, dev)
+    dg1, db1 = torch.ones(C, device=dev), torch.ones(C, device=dev)
+    dg2, db2 = torch.ones(C, device=dev), torch.ones(C, device=dev)
+    dx_a, dres_a, _ = nv.bn_bwd(dy, x, y, stat, relu, res, dg1, db1, 1.0)
+    dx_b, dres_b = nv.bn_bwd_fused(dy, x, y, stat, relu, res, dg2, db2, 1.0)
+    torch.cuda.synchronize()
+    assert _rel_err(dx_b, dx_a) < 2e-3 and _rel_err(dg2, dg1) < 1e-4 and _rel_err(db2, db1) < 1e-4
+    if res:
+        assert torch.equal(dres_a, dres_b)
