@@ -63,6 +63,7 @@ class TrainConfig:
     resume: str = ""                     # optional full checkpoint (model+optimizer+epoch)
     save_full_checkpoint: bool = False
     max_steps: int = 0                   # 0 = run whole epochs
+    trace: str = ""                      # write a Chrome-trace JSON of the training loop here (rank is appended)
     eval: bool = True
 
     @property
@@ -101,6 +102,7 @@ def add_extension_arguments(parser: argparse.ArgumentParser) -> argparse.Argumen
     parser.add_argument("--save-full-checkpoint", action="store_true")
     parser.add_argument("--max-steps", type=int, default=0)
     parser.add_argument("--no-eval", dest="eval", action="store_false", default=True)
+    parser.add_argument("--trace", type=str, default="", help="Chrome-trace JSON of the loop (host + device ranges), per rank")
     return parser
 
 

@@ -117,6 +117,8 @@ def train(cfg: TrainConfig):
         logger.info("Resumed from %s at epoch %d", cfg.resume, start_epoch)
 
     step = TrainStep(model, criterion, optimizer, batch_size, device=device, graph=cfg.graph, seed=cfg.seed + rank)
+    from ..utils.trace import Tracer
+    tracer = Tracer(rank=rank, enabled=bool(cfg.trace))
     total_steps = 0
     t_epoch_img = 0
     for epoch in range(start_epoch, cfg.epochs + 1):
@@ -125,7 +127,8 @@ def train(cfg: TrainConfig):
         seen_imgs = 0
         for batch_idx, (data, target) in enumerate(train_loader, 1):
             want = batch_idx % cfg.log_interval == 0
-            loss = step(data, target, need_loss=want)
+            with tracer.range("train_step"):
+                loss = step(data, target, need_loss=want)
             seen_imgs += len(data)
             total_steps += 1
             if want:
@@ -140,13 +143,16 @@ def train(cfg: TrainConfig):
         logger.info("Epoch %d: %.0f images/sec (all ranks, host clock, incl. data loading)", epoch, t_epoch_img)
         if cfg.eval:
             step.flush_counters()
-            ref_loss, acc, ce = evaluate(model, test_loader, device)
+            with tracer.range("evaluate"):
+                ref_loss, acc, ce = evaluate(model, test_loader, device)
             logger.info(fmt_test_line(ref_loss, acc))
             logger.info("Test set: cross-entropy: {:.4f}".format(ce))
         if cfg.max_steps and total_steps >= cfg.max_steps:
             break
 
     step.flush_counters()
+    if cfg.trace:
+        logger.info("Trace written to %s", tracer.save("%s.rank%d.json" % (cfg.trace, rank)))
     logger.info("Saving trained model only on rank 0")
     if rank == 0:
         logger.info("Saving the model.")

@@ -13,6 +13,7 @@ Differences on purpose:
 """
 from __future__ import annotations
 
+import json
 import os
 from typing import Optional
 
@@ -88,6 +89,98 @@ class SyntheticText(torch.utils.data.Dataset):
         return torch.from_numpy(self.Xs[i]), int(self.ys[i])
 
 
+# ------------------------------------------------------------------------------------------------
+# real-data loaders (model_lib/audio_dataset.py:11-34, model_lib/rtNLP_dataset.py:6-25)
+# ------------------------------------------------------------------------------------------------
+# Speech Commands v0.01 class list in directory order: the reference imports it from an `audio_preprocess` module it does
+# not ship, so it is spelled out here.
+SPEECH_ALL_CLS = ["bed", "bird", "cat", "dog", "down", "eight", "five", "four", "go", "happy", "house", "left", "marvin", "nine",
+                  "no", "off", "on", "one", "right", "seven", "sheila", "six", "stop", "three", "tree", "two", "up", "wow", "yes",
+                  "zero"]
+SPEECH_USED_CLS = ["yes", "no", "up", "down", "left", "right", "on", "off", "stop", "go"]
+
+
+class SpeechCommand(torch.utils.data.Dataset):
+    """Preprocessed Speech Commands (``{train,val,test}_data.npy`` [n,16000] + ``_label.npy``), restricted to the ten
+    command words and relabelled 0..9 -- the on-disk format of the reference's loader."""
+
+    def __init__(self, split: int, path: str = "./raw_data/speech_command/processed", all_cls=None):
+        name = {0: "train", 1: "val", 2: "test"}[split]
+        xs = np.load(os.path.join(path, "%s_data.npy" % name), mmap_mode="r")
+        ys = np.load(os.path.join(path, "%s_label.npy" % name))
+        all_cls = list(all_cls) if all_cls is not None else SPEECH_ALL_CLS
+        remap = np.full(len(all_cls), -1, dtype=np.int64)
+        for new, word in enumerate(SPEECH_USED_CLS):
+            remap[all_cls.index(word)] = new
+        keep = np.nonzero(remap[ys] >= 0)[0]
+        self.Xs = np.ascontiguousarray(xs[keep], dtype=np.float32)
+        self.ys = remap[ys[keep]]
+
+    def __len__(self):
+        return len(self.ys)
+
+    def __getitem__(self, i):
+        return torch.from_numpy(self.Xs[i]), int(self.ys[i])
+
+
+class RTNLP(torch.utils.data.Dataset):
+    """Preprocessed rt-polarity (``{train,dev}_data.npy`` int token ids, zero padded, ``_label.npy``, ``dict.json`` with
+    ``tok2idx`` / ``idx2tok``) -- the on-disk format of the reference's loader."""
+
+    def __init__(self, train: bool, path: str = "./raw_data/rt_polarity/"):
+        name = "train" if train else "dev"
+        self.Xs = np.load(os.path.join(path, "%s_data.npy" % name)).astype(np.int64)
+        self.ys = np.load(os.path.join(path, "%s_label.npy" % name)).astype(np.int64)
+        with open(os.path.join(path, "dict.json")) as fh:
+            info = json.load(fh)
+        self.tok2idx, self.idx2tok = info["tok2idx"], info["idx2tok"]
+
+    def __len__(self):
+        return len(self.ys)
+
+    def __getitem__(self, i):
+        return torch.from_numpy(self.Xs[i]), int(self.ys[i])
+
+
+def prepare_rt_polarity(raw_dir: str, out_dir: Optional[str] = None, max_len: int = 56, vocab: int = 18000, dev_fraction: float = 0.1,
+                        seed: int = 0) -> str:
+    """Build the arrays ``RTNLP`` loads from the raw ``rt-polarity.{pos,neg}`` files (the reference ships the raw text --
+    ``raw_data/rt_polarity`` -- but neither its preprocessing script nor the processed files).  Tokens are the
+    whitespace-separated lower-cased words of the (already tokenised) corpus, ids 1..vocab-1 by descending frequency, 0 pads,
+    sentences are cut / padded to ``max_len``; a seeded ``dev_fraction`` split is held out.  Returns ``out_dir``."""
+    out_dir = out_dir or raw_dir
+    sents, labels = [], []
+    for label, fname in ((1, "rt-polarity.pos"), (0, "rt-polarity.neg")):
+        with open(os.path.join(raw_dir, fname), encoding="latin-1") as fh:
+            for line in fh:
+                toks = line.lower().split()
+                if toks:
+                    sents.append(toks)
+                    labels.append(label)
+    freq: dict = {}
+    for toks in sents:
+        for t in toks:
+            freq[t] = freq.get(t, 0) + 1
+    words = sorted(freq, key=lambda w: (-freq[w], w))[: vocab - 1]
+    tok2idx = {w: i + 1 for i, w in enumerate(words)}
+    X = np.zeros((len(sents), max_len), dtype=np.int64)
+    for i, toks in enumerate(sents):
+        ids = [tok2idx[t] for t in toks if t in tok2idx][:max_len]
+        X[i, : len(ids)] = ids
+    y = np.asarray(labels, dtype=np.int64)
+    order = np.random.RandomState(seed).permutation(len(y))
+    n_dev = int(len(y) * dev_fraction)
+    dev, train = order[:n_dev], order[n_dev:]
+    os.makedirs(out_dir, exist_ok=True)
+    np.save(os.path.join(out_dir, "train_data.npy"), X[train])
+    np.save(os.path.join(out_dir, "train_label.npy"), y[train])
+    np.save(os.path.join(out_dir, "dev_data.npy"), X[dev])
+    np.save(os.path.join(out_dir, "dev_label.npy"), y[dev])
+    with open(os.path.join(out_dir, "dict.json"), "w") as fh:
+        json.dump({"tok2idx": tok2idx, "idx2tok": {str(i): w for w, i in tok2idx.items()}}, fh)
+    return out_dir
+
+
 def load_dataset_setting(task: str, root: str = "./raw_data/", synthetic_size: Optional[int] = None):
     """-> (BATCH_SIZE, N_EPOCH, trainset, testset, is_binary, need_pad, Model, troj_gen_func, random_troj_setting)."""
     if task not in MODELS:
@@ -111,11 +204,19 @@ def load_dataset_setting(task: str, root: str = "./raw_data/", synthetic_size: O
             trainset = SyntheticVision(task, True, synthetic_size)
             testset = SyntheticVision(task, False, None if synthetic_size is None else max(synthetic_size // 5, 50))
     elif task == "audio":
-        trainset = SyntheticSpeech(True, synthetic_size)
-        testset = SyntheticSpeech(False, None if synthetic_size is None else max(synthetic_size // 5, 50))
+        proc = os.path.join(root, "speech_command", "processed")
+        if synthetic_size is None and os.path.exists(os.path.join(proc, "train_data.npy")):
+            trainset, testset = SpeechCommand(0, proc), SpeechCommand(2, proc)
+        else:
+            trainset = SyntheticSpeech(True, synthetic_size)
+            testset = SyntheticSpeech(False, None if synthetic_size is None else max(synthetic_size // 5, 50))
     else:
-        trainset = SyntheticText(True, synthetic_size)
-        testset = SyntheticText(False, None if synthetic_size is None else max(synthetic_size // 5, 50))
+        proc = os.path.join(root, "rt_polarity")
+        if synthetic_size is None and os.path.exists(os.path.join(proc, "train_data.npy")):
+            trainset, testset = RTNLP(True, proc), RTNLP(False, proc)
+        else:
+            trainset = SyntheticText(True, synthetic_size)
+            testset = SyntheticText(False, None if synthetic_size is None else max(synthetic_size // 5, 50))
     Model = MODELS[task]
     return (batch, n_epoch, trainset, testset, is_binary, need_pad, Model, T.troj_gen_func(task),
             lambda troj_type, rng=np.random: T.random_troj_setting(task, troj_type, rng))

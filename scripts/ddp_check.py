@@ -57,6 +57,8 @@ def main():
     # and resnet18 at init amplifies that to ~20% in the early-layer gradients.  The two passes compared here
     # must be reproducible, so split-K is off for this part (it is back on for the training steps below).
     nv.SPLIT_K[0] = False
+    from b200ddp.nn import modules as bmod
+    fuse_stats, bmod._FUSE_BN_STATS[0] = bmod._FUSE_BN_STATS[0], False      # BN sums through red.add: same story as split-K
     with model.no_sync():
         fwd_bwd()
     torch.cuda.synchronize()
@@ -79,6 +81,7 @@ def main():
     print_ok("synced grads == mean(local grads) (rel %.2e)" % rel, rel < 2e-2)
     ok &= eq_ranks and rel < 2e-2
     nv.SPLIT_K[0] = True
+    bmod._FUSE_BN_STATS[0] = fuse_stats
     if rank == 0:
         print("allreduce algorithms used:", sorted(set(model.comm.launch_log)), flush=True)
 

@@ -187,3 +187,42 @@ def test_sass_has_blackwell_tensor_core_and_multimem_instructions():
     assert "UTCHMMA" in sass and "LDTM" in sass and "LDGSTS" in sass
     ptx_or_sass = subprocess.run(["cuobjdump", "-sass", os.path.join(ROOT, "build", "comm.o")], capture_output=True, text=True).stdout
     assert "LDGMC" in ptx_or_sass            # SASS of multimem.ld_reduce (multimem.st shows as a multicast STG)
+
+
+def test_tracer_writes_chrome_trace_and_trainer_flag(tmp_path):
+    from b200ddp.utils.config import parse_args
+    from b200ddp.utils.trace import Tracer
+    tr = Tracer(rank=3)
+    with tr.range("outer"):
+        with tr.range("inner"):
+            sum(range(1000))
+    path = tr.save(str(tmp_path / "t.json"))
+    ev = json.load(open(path))["traceEvents"]
+    names = [e["name"] for e in ev if e["ph"] == "X"]
+    assert "outer" in names and "inner" in names and all(e["pid"] == 3 for e in ev)
+    outer = [e for e in ev if e["name"] == "outer" and e["ph"] == "X"][0]
+    inner = [e for e in ev if e["name"] == "inner" and e["ph"] == "X"][0]
+    assert outer["dur"] >= inner["dur"] and inner["args"]["depth"] == 1
+    assert set(tr.summary_ms()) == {"outer", "inner"}
+    assert parse_args(["--trace", "/tmp/x"]).trace == "/tmp/x"
+    off = Tracer(enabled=False)
+    with off.range("x"):
+        pass
+    assert off.summary_ms() == {}
+
+
+def test_pipeline_api_falls_back_to_plain_steps_on_cpu():
+    from b200ddp.models import get_model
+    from b200ddp.nn import CrossEntropyLoss
+    from b200ddp.ops import functional as BF
+    from b200ddp.runtime.engine import TrainStep
+    torch.manual_seed(0)
+    net = get_model("custom")
+    opt = torch.optim.SGD(net.parameters(), lr=0.05)
+    step = TrainStep(net, CrossEntropyLoss(), opt, 8, device=torch.device("cpu"), graph=True, augment=False)
+    xs = torch.randint(0, 256, (3, 8, 32, 32, 3), dtype=torch.uint8)
+    ys = torch.randint(0, 10, (3, 8))
+    losses = list(step.pipeline((xs[i], ys[i]) for i in range(3)))
+    assert len(losses) == 3 and all(isinstance(v, float) and v == v for v in losses) and step.steps_done == 3
+    x = torch.randn(2, 3, 8, 8, requires_grad=True)
+    assert BF.fork(x) is x and not hasattr(x, "_b200_mailbox")          # CPU tensors are never forked

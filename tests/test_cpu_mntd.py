@@ -174,3 +174,44 @@ def test_meta_classifier_oc_variant():
     assert np.isfinite(loss) and isinstance(oc.r, float)
     auc, acc = UM.epoch_meta_eval_oc(oc, MNISTModel(), [(paths[0][0], 1), (paths[1][0], 0)], False, threshold="half")
     assert 0.0 <= acc <= 1.0
+
+
+@needs_ref
+def test_rt_polarity_is_prepared_from_the_shipped_raw_text_and_trains(tmp_path):
+    """The reference ships raw rt-polarity text but not its processed arrays: prepare_rt_polarity builds the
+    arrays RTNLP loads, load_dataset_setting picks them up, and the text CNN fits a few real sentences."""
+    from b200ddp.workloads.mntd import basic as UB
+    raw = os.path.join(REF_CODE, "raw_data", "rt_polarity")
+    out = UB.prepare_rt_polarity(raw, str(tmp_path / "rt_polarity"))
+    tr, dev = UB.RTNLP(True, out), UB.RTNLP(False, out)
+    assert len(tr) + len(dev) == 10662 and len(dev) == 1066 and tr.Xs.shape[1] == 56
+    assert 0 < int(tr.Xs.max()) < 18000 and set(np.unique(tr.ys)) == {0, 1}
+    assert tr.idx2tok[str(tr.tok2idx["film"])] == "film"
+    x0, y0 = tr[0]
+    assert x0.dtype == torch.long and y0 in (0, 1)
+    _, _, trainset, testset, is_binary, need_pad, Model, _, _ = UB.load_dataset_setting("rtNLP", root=str(tmp_path))
+    assert isinstance(trainset, UB.RTNLP) and is_binary and need_pad and len(testset) == 1066
+    torch.manual_seed(0)
+    model = Model(emb_path="")
+    sub = torch.utils.data.Subset(trainset, range(64))
+    loader = UB.make_loader(sub, 32, shuffle=False)
+    before = UB.eval_model(model, loader, True)
+    UB.train_model(model, loader, 25, True, verbose=False, lr=1e-3)
+    assert UB.eval_model(model, loader, True) > max(before, 0.9)
+
+
+def test_speech_command_loader_reads_the_reference_npy_layout(tmp_path):
+    from b200ddp.workloads.mntd import basic as UB
+    proc = tmp_path / "speech_command" / "processed"
+    proc.mkdir(parents=True)
+    rng = np.random.RandomState(0)
+    for split, n in (("train", 40), ("val", 8), ("test", 12)):
+        np.save(proc / ("%s_data.npy" % split), rng.normal(0, 0.1, size=(n, 16000)).astype(np.float32))
+        np.save(proc / ("%s_label.npy" % split), rng.randint(0, 30, size=n))
+    ds = UB.SpeechCommand(0, str(proc))
+    labels = np.load(proc / "train_label.npy")
+    keep = [i for i, y in enumerate(labels) if UB.SPEECH_ALL_CLS[y] in UB.SPEECH_USED_CLS]
+    assert len(ds) == len(keep) and all(0 <= ds[i][1] < 10 for i in range(len(ds)))
+    assert UB.SPEECH_USED_CLS[ds[0][1]] == UB.SPEECH_ALL_CLS[labels[keep[0]]] and ds[0][0].shape == (16000,)
+    _, _, trainset, testset, is_binary, _, _, _, _ = UB.load_dataset_setting("audio", root=str(tmp_path))
+    assert isinstance(trainset, UB.SpeechCommand) and isinstance(testset, UB.SpeechCommand) and not is_binary
