@@ -185,7 +185,7 @@ class NativeReducer:
         cnts = (c_size_t * nb)(*[b.numel for b in buckets])
         cfg = comm.cfg
         self._h = lib.b200_reducer_create(byref(comm.cs), c_int(n), pb, c_int(nb), offs, cnts, c_int(L.DTYPE_F32),
-                                          c_float(1.0 / world_size), c_int(cfg.max_ctas), c_size_t(cfg.oneshot_max_bytes),
+                                          c_float(1.0 / world_size), c_int(cfg.overlap_ctas), c_size_t(cfg.oneshot_max_bytes),
                                           c_size_t(cfg.nvls_min_bytes if (comm.has_nvls and comm.prefer_nvls) else (1 << 62)))
         if not self._h:
             raise L.NativeError("b200_reducer_create failed: %s" % lib.b200_last_error().decode())

@@ -224,7 +224,8 @@ class SymmComm:
             return L.ALGO_NVLS
         return L.ALGO_TWOSHOT
 
-    def _launch_allreduce(self, offset: int, numel: int, dtype: torch.dtype, scale: float, stream, algo: int = 0):
+    def _launch_allreduce(self, offset: int, numel: int, dtype: torch.dtype, scale: float, stream, algo: int = 0,
+                          max_ctas: Optional[int] = None):
         nbytes = numel * _ELEM[dtype]
         if algo == L.ALGO_AUTO:
             algo = self.pick_algo(nbytes)
@@ -232,7 +233,7 @@ class SymmComm:
             log.debug("b200ddp allreduce: %d bytes at +%d -> %s", nbytes, offset, L.ALGO_NAMES[algo])
         self.launch_log.append((L.ALGO_NAMES[algo], nbytes))
         L.check(self.lib.b200_allreduce(byref(self.cs), c_size_t(offset), c_size_t(numel), c_int(L.dtype_code(dtype)),
-                                        ctypes.c_float(scale), c_int(algo), c_int(self.cfg.max_ctas), L.stream_ptr(stream)),
+                                        ctypes.c_float(scale), c_int(algo), c_int(max_ctas or self.cfg.max_ctas), L.stream_ptr(stream)),
                 "allreduce")
 
     def all_reduce_arena(self, offset_bytes: int, numel: int, scale: float = 1.0, dtype: torch.dtype = torch.float32,
@@ -250,7 +251,7 @@ class SymmComm:
                 ev = torch.cuda.Event()
                 ev.record(other)
                 self.comm_stream.wait_event(ev)
-            self._launch_allreduce(offset_bytes, numel, dtype, scale, self.comm_stream, algo)
+            self._launch_allreduce(offset_bytes, numel, dtype, scale, self.comm_stream, algo, self.cfg.overlap_ctas)
             self._overlap_dirty = True
         else:
             self._launch_allreduce(offset_bytes, numel, dtype, scale, torch.cuda.current_stream(self.device), algo)

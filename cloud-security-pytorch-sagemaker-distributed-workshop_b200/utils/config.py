@@ -141,6 +141,9 @@ class CommConfig:
     oneshot_max_bytes: int = env_int("B200DDP_ONESHOT_MAX_BYTES", 64 * 1024)
     nvls_min_bytes: int = env_int("B200DDP_NVLS_MIN_BYTES", 64 * 1024)
     use_nvls: bool = env_flag("B200DDP_NVLS", True)
-    max_ctas: int = env_int("B200DDP_COMM_CTAS", 64)
+    max_ctas: int = env_int("B200DDP_COMM_CTAS", 64)          # stand-alone collectives: whatever gives peak bandwidth
+    # Bucket all-reduces that overlap the backward pass get a small SM budget so the compute kernels keep the machine:
+    # resnet18, global batch 256 on 4 x B200: 64 / 24 / 8 CTAs -> 0.943 / 0.914 / 0.877 ms per step.
+    overlap_ctas: int = env_int("B200DDP_OVERLAP_CTAS", 8)
     spin_timeout_ms: int = env_int("B200DDP_SPIN_TIMEOUT_MS", 20000)
     debug: bool = os.environ.get("B200DDP_DEBUG", "").upper() in ("INFO", "1", "TRACE")
