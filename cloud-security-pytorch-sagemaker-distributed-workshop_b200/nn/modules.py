@@ -27,23 +27,24 @@ class Conv2d(nn.Conv2d):
         if self.stride[0] != self.stride[1] or self.padding[0] != self.padding[1]:
             raise ValueError("b200ddp.nn.Conv2d supports symmetric stride/padding only")
         self.fused_relu = relu
-        self._bn_pair = None          # weakref to the BatchNorm2d that consumes this conv's output (fuse_bn_stats)
+        # the BatchNorm2d that consumes this conv's output (fuse_bn_stats).  Set with object.__setattr__ so that it is NOT
+        # registered as a child module (state_dict keys stay torch's) while deepcopy / pickle still carry the pairing along.
+        object.__setattr__(self, "_bn_pair", None)
         self._bn_sums = None
 
     def fuse_bn_stats(self, bn: "BatchNorm2d"):
         """Declare that ``bn`` normalises exactly this conv's output.  In training mode on CUDA the conv epilogue then
         accumulates the per-channel sum / sum of squares (fp32) and ``bn`` skips its own statistics pass over the tensor."""
-        import weakref
         if self.bias is not None or self.fused_relu:
             raise ValueError("fuse_bn_stats needs a conv without bias and without fused ReLU")
-        self._bn_pair = weakref.ref(bn)
+        object.__setattr__(self, "_bn_pair", bn)
         return self
 
     def forward(self, x):
         if not x.is_cuda:
             return BF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0], self.fused_relu)
         x = BF.as_activation(x)
-        bn = self._bn_pair() if self._bn_pair is not None else None
+        bn = self._bn_pair
         if bn is not None and self.training and bn.training and _FUSE_BN_STATS[0]:
             n, _, h, w = x.shape
             ho = (h + 2 * self.padding[0] - self.kernel_size[0]) // self.stride[0] + 1

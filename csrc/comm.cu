@@ -16,29 +16,21 @@
 //   broadcast (W4)  pull from the root's arena.       barrier (W5)  flag exchange on the signal pads.
 //
 // Synchronisation: per-CTA flag barrier on the signal pads (first MiB of every arena).  Block b of rank
-// a writes epoch e into slot [e&1][b][a] of every peer (st.release.sys) and spins on its own slots
-// (ld.acquire.sys) until all peers wrote e.  Epochs live in device memory, so the kernels are CUDA-graph
-// replayable.  A spin that exceeds timeout_ns raises the host-mapped error flag and falls through
+// a writes epoch e into slot [e&1][b][a] of every peer and spins on its own slots until all peers wrote e:
+// relaxed system-scope flag stores / loads, with a release fence before the store only where the CTA has pushed
+// data into peer memory and an acquire fence after the spin (a system-scope fence per poll cost microseconds).
+// Epochs live in device memory, so the kernels are CUDA-graph replayable.  A spin that exceeds timeout_ns raises the host-mapped error flag and falls through
 // instead of hanging (SURVEY §5.3 failure detection).
 #include "common.cuh"
 
 namespace {
 
 constexpr int kThreads = 512;
-constexpr int kSigInts = 2 * B200_MAX_COMM_BLOCKS * B200_MAX_RANKS;  // flags region, uint32
-// layout of the signal MiB:  [0, kSigInts*4) flags | [64 KiB, 64 KiB + blocks*4) epochs (local only)
+// layout of the signal MiB:  [0, 2 * B200_MAX_COMM_BLOCKS * B200_MAX_RANKS * 4) flags (uint32) | [64 KiB, 64 KiB + blocks*4) epochs (local only)
 constexpr size_t kEpochOff = 64 * 1024;
 
 __device__ __forceinline__ uint32_t* sig_slot(char* base, uint32_t phase, int block, int src) {
   return reinterpret_cast<uint32_t*>(base) + ((phase * B200_MAX_COMM_BLOCKS + block) * B200_MAX_RANKS + src);
-}
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
 }
 __device__ __forceinline__ unsigned long long globaltimer_ns() {
   unsigned long long t;

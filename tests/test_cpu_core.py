@@ -226,3 +226,18 @@ def test_pipeline_api_falls_back_to_plain_steps_on_cpu():
     assert len(losses) == 3 and all(isinstance(v, float) and v == v for v in losses) and step.steps_done == 3
     x = torch.randn(2, 3, 8, 8, requires_grad=True)
     assert BF.fork(x) is x and not hasattr(x, "_b200_mailbox")          # CPU tensors are never forked
+
+
+def test_conv_bn_pairing_survives_deepcopy_and_keeps_state_dict_keys():
+    import copy
+    import torchvision
+    from b200ddp.models import get_model
+    m = get_model("resnet18")
+    c = copy.deepcopy(m)
+    blk, cblk = m.layer2[0], c.layer2[0]
+    assert blk.conv1._bn_pair is blk.bn1 and blk.downsample[0]._bn_pair is blk.downsample[1] and m.conv1._bn_pair is m.bn1
+    assert cblk.conv2._bn_pair is cblk.bn2 and cblk.conv2._bn_pair is not blk.bn2         # the copy pairs with ITS BatchNorm
+    assert len(list(blk.conv1.children())) == 0                                           # not registered as a child module
+    assert list(c.state_dict().keys()) == list(torchvision.models.resnet18().state_dict().keys())
+    x = torch.randn(2, 3, 32, 32)
+    assert torch.allclose(m.eval()(x), c.eval()(x))
