@@ -275,3 +275,19 @@ def test_pipelined_steps_equal_sequential_steps(pg):
     # ordering would show up at the 1e-2 level
     assert len(b[0]) == 6 and all(abs(u - v) < 2e-4 for u, v in zip(a[0], b[0])), (a[0], b[0])
     assert _rel(b[1], a[1]) < 2e-4
+
+
+@pytest.mark.parametrize("task", ["mnist", "audio", "rtNLP"])
+def test_mntd_zoo_trainer_and_meta_classifier_on_gpu(task, tmp_path):
+    """The MNTD pipeline end to end on the GPU (gpu=True): trojaned shadow models trained through the native kernels
+    (tensor-core convs / FFT mel + LSTM / text CNN, GPU trojan stamping), then the meta-classifier with query tuning --
+    whose gradient flows through the shadow model into the input queries."""
+    from b200ddp.workloads.mntd import run_meta, train_basic
+    _dev()
+    root = str(tmp_path / "ckpt")
+    for kind in ("benign", "jumbo", "trojaned"):
+        log = train_basic.run(kind, task, "M", gpu=True, save_root=root, num=2, epochs=1, synthetic_size=160, seed=1)
+        assert log["models"] >= 2 and 0.0 <= log["acc"] <= 1.0
+    auc = run_meta.run(task, "M", gpu=True, shadow_root=root, save_root=str(tmp_path / "meta"), n_repeat=1, n_epoch=1,
+                       train_num=1, val_num=1, test_num=2, verbose=False)
+    assert 0.0 <= auc <= 1.0
