@@ -75,6 +75,13 @@ class TrainStep:
         off = np.stack([self.rng.randint(0, 9, n), self.rng.randint(0, 9, n), self.rng.randint(0, 2, n)], 1)
         return torch.from_numpy(off.astype(np.int32))
 
+    def _draw_offsets_into(self, pinned_np: np.ndarray) -> None:
+        """Same draws, same order as ``_draw_offsets``, written straight into a pinned [B,3] int32 buffer."""
+        n = pinned_np.shape[0]
+        pinned_np[:, 0] = self.rng.randint(0, 9, n)
+        pinned_np[:, 1] = self.rng.randint(0, 9, n)
+        pinned_np[:, 2] = self.rng.randint(0, 2, n)
+
     def _body(self, x_u8, y, offsets):
         from ..ops import native as nv
         if self.cuda and self._net_mega is not None:
@@ -175,6 +182,7 @@ class TrainStep:
                 "ready": [torch.cuda.Event() for _ in range(2)],
             }
             self._pipe["views"] = [self._views(b) for b in self._pipe["stage"]]
+            self._pipe["pin_off_np"] = [t.numpy() for t in self._pipe["pin_off"]]
         P = self._pipe
         cur = torch.cuda.current_stream(dev)
         pending = None                       # slot whose loss has not been yielded yet
@@ -198,7 +206,7 @@ class TrainStep:
                 sx.copy_(x, non_blocking=True)
                 sy.copy_(y, non_blocking=True)
                 if self.augment:
-                    P["pin_off"][slot].copy_(self._draw_offsets(self.batch_size))
+                    self._draw_offsets_into(P["pin_off_np"][slot])
                     so.copy_(P["pin_off"][slot], non_blocking=True)
                 P["h2d"][slot].record(P["cs"])
             cur.wait_event(P["h2d"][slot])
