@@ -163,15 +163,18 @@ class _Conv2dFn(torch.autograd.Function):
                 mb.grads.append(nv.conv_dgrad(dy, w, x.shape, stride, pad))
         dw = None
         if weight.requires_grad:
+            # a conv whose input needs no gradient is the network's first layer: its wgrad is the tail of the backward
+            # pass with nothing beside it, so it may split over (almost) the whole machine: 32 clusters of 4 = one wave
+            alone = -85 if not ctx.needs_input_grad[0] else 0
             exact = (Cp == C and Kp == K)
             sink = getattr(weight, "_b200_sink", None)
             if exact and sink is not None:
                 with streams.forked(x.device, x, dy):        # off the dgrad critical path
-                    nv.conv_wgrad_(sink.flat.view(K, R, S, C), x, dy, stride, pad)
+                    nv.conv_wgrad_(sink.flat.view(K, R, S, C), x, dy, stride, pad, alone)
                     sink.done()
             else:
                 tmp = torch.zeros((Kp, R, S, Cp), dtype=torch.float32, device=x.device)
-                nv.conv_wgrad_(tmp, x, dy, stride, pad)
+                nv.conv_wgrad_(tmp, x, dy, stride, pad, alone)
                 dw = tmp[:K, :, :, :C].permute(0, 3, 1, 2)
                 if sink is not None:
                     sink.flat.view(K, R, S, C).add_(tmp[:K, :, :, :C])

@@ -835,7 +835,10 @@ extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b
   // one (~11 us) and leave SMs to the dgrad / BN kernels that run concurrently on the main stream.  The `zc` CTAs of a
   // cluster reduce through DSMEM so only one red.add per element leaves the cluster; `zo` clusters meet in the atomics.
   static const uint32_t sm_pct = []() { const char* e = getenv("B200DDP_WGRAD_SM_PCT"); const int v = e ? atoi(e) : 60; return (uint32_t)(v < 1 ? 1 : v); }();
-  uint32_t splits = ((uint32_t)b200_num_sms() * sm_pct / 100u) / tiles;
+  // max_splits < 0: the caller knows nothing runs next to this wgrad (the first layer's, at the tail of backward) and
+  // gives the SM share to use as -percent
+  const uint32_t pct = max_splits < 0 ? (uint32_t)(-max_splits) : sm_pct;
+  uint32_t splits = ((uint32_t)b200_num_sms() * pct / 100u) / tiles;
   if (max_splits > 0 && splits > (uint32_t)max_splits) splits = (uint32_t)max_splits;
   const uint32_t max_by_k = (kblocks + 1) / 2;
   if (splits > max_by_k) splits = max_by_k;

@@ -234,6 +234,8 @@ int b200_bn_apply_sums(const void* x_bf16, const void* residual_bf16, void* y_bf
 int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream);
 /* dx = dgrad(dy, w) + residual: the gradient of the other branch of a forked tensor (ResNet skip) added in the epilogue */
 int b200_conv_dgrad_add(const void* dy, const void* w, void* dx, const b200_conv_geom* g, const void* residual, void* stream);
+/* dw (fp32, accumulated into) += wgrad(x, dy).  max_splits: 0 = automatic (the reduction over positions is split over
+   ~60 % of the SMs), > 0 = cap on the number of splits, < 0 = use -max_splits percent of the SMs (nothing runs alongside) */
 int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
                     void* stream);
 
