@@ -121,6 +121,7 @@ class TrainStep:
             loss = self._body(self.static_x, self.static_y, self.static_off)
             self.static_loss.copy_(loss)
         self._graph = g
+        self._pipe_init()
         self.steps_done += self.warmup_iters       # warm-up iterations were real optimizer steps
 
     # ------------------------------------------------------------------ public
@@ -170,19 +171,7 @@ class TrainStep:
                 yield self(x, y, need_loss=need_loss)
             return
         dev = self.device
-        if not hasattr(self, "_pipe"):
-            cs = torch.cuda.Stream(device=dev)
-            self._pipe = {
-                "cs": cs,
-                "stage": [torch.zeros_like(self.static_blob) for _ in range(2)],
-                "pin_off": [torch.zeros((self.batch_size, 3), dtype=torch.int32).pin_memory() for _ in range(2)],
-                "pin_loss": [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)],
-                "h2d": [torch.cuda.Event() for _ in range(2)],
-                "free": [torch.cuda.Event() for _ in range(2)],
-                "ready": [torch.cuda.Event() for _ in range(2)],
-            }
-            self._pipe["views"] = [self._views(b) for b in self._pipe["stage"]]
-            self._pipe["pin_off_np"] = [t.numpy() for t in self._pipe["pin_off"]]
+        self._pipe_init()
         P = self._pipe
         cur = torch.cuda.current_stream(dev)
         pending = None                       # slot whose loss has not been yielded yet
@@ -225,6 +214,23 @@ class TrainStep:
         if pending is not None:
             P["ready"][pending].synchronize()
             yield float(P["pin_loss"][pending].item()) if need_loss else None
+
+    def _pipe_init(self):
+        """Staging blobs, pinned offset / loss slots, copy stream and events of ``pipeline`` (allocated once, at capture)."""
+        dev = self.device
+        if not hasattr(self, "_pipe"):
+            cs = torch.cuda.Stream(device=dev)
+            self._pipe = {
+                "cs": cs,
+                "stage": [torch.zeros_like(self.static_blob) for _ in range(2)],
+                "pin_off": [torch.zeros((self.batch_size, 3), dtype=torch.int32).pin_memory() for _ in range(2)],
+                "pin_loss": [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)],
+                "h2d": [torch.cuda.Event() for _ in range(2)],
+                "free": [torch.cuda.Event() for _ in range(2)],
+                "ready": [torch.cuda.Event() for _ in range(2)],
+            }
+            self._pipe["views"] = [self._views(b) for b in self._pipe["stage"]]
+            self._pipe["pin_off_np"] = [t.numpy() for t in self._pipe["pin_off"]]
 
     def flush_counters(self):
         if self.cuda:
