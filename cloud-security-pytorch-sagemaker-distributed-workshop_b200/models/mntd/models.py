@@ -159,10 +159,9 @@ class AudioModel(_Base):
     def forward(self, x):
         x = self._in(x)
         if x.is_cuda:
-            # native path: FFT + mel + dB in one kernel, LSTM recurrence with W_hh in registers.
-            # A waveform that needs its own gradient (meta-classifier query tuning) goes through the torch.stft features.
-            from ...ops import native as nv
-            feats = self.features(x) if x.requires_grad else nv.mel_frontend(x.float().contiguous(), self._window, self._mel)
+            # native path: FFT + mel + dB in one kernel (with its backward to the waveform, which the
+            # meta-classifier's query tuning needs), LSTM recurrence with W_hh in registers
+            feats = BF.mel_features(x, self._window, self._mel)
             lstm_out = BF.lstm(feats, self.lstm)
             att = BF.linear_f32(lstm_out, self.lstm_att.weight, self.lstm_att.bias).squeeze(2)
             emb = (lstm_out * F.softmax(att, dim=1).unsqueeze(2)).sum(1)

@@ -554,6 +554,25 @@ def linear_f32(x, w, b=None):
     return _LinearF32Fn.apply(x.float(), w, b)
 
 
+class _MelFn(torch.autograd.Function):
+    """Waveform -> normalised log-mel features (FFT kernel), with the gradient back to the waveform for query tuning."""
+
+    @staticmethod
+    def forward(ctx, x, window, melfb):
+        x = x.float().contiguous()
+        ctx.save_for_backward(x, window, melfb)
+        return nv.mel_frontend(x, window, melfb)
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, window, melfb = ctx.saved_tensors
+        return nv.mel_frontend_bwd(x, window, melfb, dout.float().contiguous()), None, None
+
+
+def mel_features(x, window, melfb):
+    return _MelFn.apply(x, window, melfb)
+
+
 class _LSTMLayerFn(torch.autograd.Function):
     """One ``nn.LSTM`` layer (batch_first, zero initial state): input projection as one GEMM over [B*T], the recurrence in
     ``lstm_rec_fwd`` (W_hh rows in registers), BPTT in ``lstm_rec_bwd`` followed by three GEMMs for dW_ih, dW_hh, dx."""

@@ -490,6 +490,16 @@ def mel_frontend(x: torch.Tensor, window: torch.Tensor, melfb: torch.Tensor) -> 
     return out
 
 
+def mel_frontend_bwd(x: torch.Tensor, window: torch.Tensor, melfb: torch.Tensor, dout: torch.Tensor) -> torch.Tensor:
+    """Gradient of ``mel_frontend`` w.r.t. the waveforms: [B,L]."""
+    B, Ls = x.shape
+    assert x.is_contiguous() and dout.is_contiguous() and tuple(dout.shape) == (B, 1 + Ls // 512, melfb.shape[0])
+    dx = torch.zeros_like(x)
+    L.check(L.lib().b200_mel_frontend_bwd(L.ptr(x), L.ptr(window), L.ptr(melfb.contiguous()), L.ptr(dout), L.ptr(dx), c_int(B),
+                                          c_int(Ls), c_int(melfb.shape[0]), L.stream_ptr()), "mel_frontend_bwd")
+    return dx
+
+
 def gather_rows(table: torch.Tensor, idx: torch.Tensor, pad_rows: int = 0) -> torch.Tensor:
     """``table[idx]`` for an int64 index tensor of any shape -> [idx.numel() + pad_rows, dim] (the pad rows are zero)."""
     from ctypes import c_longlong

@@ -239,6 +239,86 @@ mel_frontend_kernel(const float* __restrict__ x, const float* __restrict__ windo
   }
 }
 
+// Backward of the mel front end w.r.t. the waveform (the meta-classifier tunes input queries through the shadow model,
+// meta_classifier.py:13,21-24).  Per frame: recompute X = FFT(frame * window) and the mel powers, then
+//   dmel[m] = dout[m] * (10 / ln 10) / 50 / mel[m]            (0 where the 1e-10 clamp is active)
+//   dpw[k]  = sum_m fb[m][k] dmel[m],   G[k] = 2 dpw[k] X[k]  (k <= N/2, 0 above: only those bins reach the output)
+//   d(frame*window)[n] = Re sum_k G[k] e^{+2 pi i k n / N}     (the same radix-2 network with conjugated twiddles)
+// and scatter-add dframe[n] * window[n] through the reflect padding into dx (atomics: frames overlap 4x).
+__device__ __forceinline__ void fft_inplace(float2* a, const float2* tw, bool conj, int tid) {
+#pragma unroll 1
+  for (int s = 1; s <= LOGN; ++s) {
+    const int half = 1 << (s - 1);
+    for (int idx = tid; idx < NFFT / 2; idx += 256) {
+      const int grp = idx >> (s - 1), pos = idx & (half - 1);
+      const int i0 = (grp << s) + pos, i1 = i0 + half;
+      float2 w = tw[pos << (LOGN - s)];
+      if (conj) w.y = -w.y;
+      const float2 u = a[i0], v = a[i1];
+      const float2 t = make_float2(w.x * v.x - w.y * v.y, w.x * v.y + w.y * v.x);
+      a[i0] = make_float2(u.x + t.x, u.y + t.y);
+      a[i1] = make_float2(u.x - t.x, u.y - t.y);
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(256)
+mel_frontend_bwd_kernel(const float* __restrict__ x, const float* __restrict__ window, const float* __restrict__ melfb,
+                        const float* __restrict__ dout, float* __restrict__ dx, int L, int frames, int n_mels) {
+  __shared__ float2 a[NFFT];
+  __shared__ float2 g[NFFT];
+  __shared__ float2 tw[NFFT / 2];
+  __shared__ float pw[NBIN + 3];
+  __shared__ float dmel[64];
+  const int f = blockIdx.x, b = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int k = tid; k < NFFT / 2; k += 256) {
+    float s, c;
+    sincospif(-(float)k / (float)(NFFT / 2), &s, &c);
+    tw[k] = make_float2(c, s);
+  }
+  const float* xb = x + (size_t)b * L;
+  for (int n = tid; n < NFFT; n += 256) {
+    int src = f * HOP - NFFT / 2 + n;
+    if (src < 0) src = -src;
+    if (src >= L) src = 2 * (L - 1) - src;
+    a[__brev((unsigned)n) >> (32 - LOGN)] = make_float2(xb[src] * window[n], 0.f);
+  }
+  __syncthreads();
+  fft_inplace(a, tw, false, tid);
+  for (int k = tid; k < NBIN; k += 256) pw[k] = a[k].x * a[k].x + a[k].y * a[k].y;
+  __syncthreads();
+  for (int m = warp; m < n_mels; m += 8) {
+    const float* fb = melfb + (size_t)m * NBIN;
+    float acc = 0.f;
+    for (int k = lane; k < NBIN; k += 32) acc = fmaf(__ldg(fb + k), pw[k], acc);
+    acc = warp_sum(acc);
+    if (lane == 0) {
+      const float go = dout[((size_t)b * frames + f) * n_mels + m];
+      dmel[m] = acc > 1e-10f ? go * (10.f / 2.302585093f / 50.f) / acc : 0.f;
+    }
+  }
+  __syncthreads();
+  for (int k = tid; k < NFFT; k += 256) {                     // G in bit-reversed order, ready for the in-place network
+    float2 v = make_float2(0.f, 0.f);
+    if (k < NBIN) {
+      float d = 0.f;
+      for (int m = 0; m < n_mels; ++m) d = fmaf(__ldg(melfb + (size_t)m * NBIN + k), dmel[m], d);
+      v = make_float2(2.f * d * a[k].x, 2.f * d * a[k].y);
+    }
+    g[__brev((unsigned)k) >> (32 - LOGN)] = v;
+  }
+  __syncthreads();
+  fft_inplace(g, tw, true, tid);
+  float* dxb = dx + (size_t)b * L;
+  for (int n = tid; n < NFFT; n += 256) {
+    int src = f * HOP - NFFT / 2 + n;
+    if (src < 0) src = -src;
+    if (src >= L) src = 2 * (L - 1) - src;
+    atomicAdd(dxb + src, g[n].x * window[n]);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // text CNN pieces
 // ------------------------------------------------------------------------------------------------
@@ -337,6 +417,17 @@ extern "C" int b200_mel_frontend(const float* x, const float* window, const floa
   B200_REQUIRE(L > NFFT / 2, "clip shorter than the reflect padding (1024 samples)");
   const int frames = 1 + L / HOP;
   mel_frontend_kernel<<<dim3(frames, B), 256, 0, (cudaStream_t)stream>>>(x, window, melfb, out, L, frames, n_mels);
+  B200_CHECK_LAUNCH();
+  return 0;
+}
+
+// dx [B][L] (zeroed by the caller, accumulated into) = d(loss)/d(waveform) given dout [B][1 + L/512][n_mels]
+extern "C" int b200_mel_frontend_bwd(const float* x, const float* window, const float* melfb, const float* dout, float* dx,
+                                     int B, int L, int n_mels, void* stream) {
+  B200_REQUIRE(x && window && melfb && dout && dx && B > 0 && n_mels > 0 && n_mels <= 64, "bad mel_frontend_bwd argument");
+  B200_REQUIRE(L > NFFT / 2, "clip shorter than the reflect padding (1024 samples)");
+  const int frames = 1 + L / HOP;
+  mel_frontend_bwd_kernel<<<dim3(frames, B), 256, 0, (cudaStream_t)stream>>>(x, window, melfb, dout, dx, L, frames, n_mels);
   B200_CHECK_LAUNCH();
   return 0;
 }

@@ -251,6 +251,9 @@ int b200_lstm_rec_bwd(const float* dh, const float* gates, const float* cseq, co
 /* waveform [B][L] -> (10 log10(mel power) + 50) / 50, [B][1 + L/512][n_mels]; 2048-point Hann STFT, hop 512, reflect */
 int b200_mel_frontend(const float* x, const float* window, const float* melfb, float* out, int B, int L, int n_mels,
                       void* stream);
+/* gradient w.r.t. the waveform, accumulated into dx [B][L] (zero it first) */
+int b200_mel_frontend_bwd(const float* x, const float* window, const float* melfb, const float* dout, float* dx, int B,
+                          int L, int n_mels, void* stream);
 int b200_gather_rows(const float* table, const int64_t* idx, float* out, long long rows, int dim, long long vocab,
                      void* stream);
 /* bias + ReLU + max-over-time of a [B*L][N] conv-as-GEMM output (window length k), and its backward */

@@ -494,3 +494,26 @@ def test_batchnorm_backward_cluster_kernel_matches_two_pass(shape, relu, res):
     assert _rel_err(dx_b, dx_a) < 2e-3 and _rel_err(dg2, dg1) < 1e-4 and _rel_err(db2, db1) < 1e-4
     if res:
         assert torch.equal(dres_a, dres_b)
+
+
+def test_mel_frontend_backward_matches_torch_autograd():
+    """d(features)/d(waveform) of the FFT kernel == autograd through torch.stft on the CPU (query tuning of the audio model)."""
+    from b200ddp.models.mntd import AudioModel
+    from b200ddp.ops import functional as BF
+    dev = _dev()
+    torch.manual_seed(9)
+    m = AudioModel()
+    x = torch.randn(3, 16000) * 0.1
+    wgt = torch.randn(3, 32, 40)
+    xr = x.clone().requires_grad_(True)
+    (m.features(xr) * wgt).sum().backward()
+    xg = x.to(dev).requires_grad_(True)
+    out = BF.mel_features(xg, m._window.to(dev), m._mel.to(dev))
+    (out * wgt.to(dev)).sum().backward()
+    torch.cuda.synchronize()
+    assert _rel(xg.grad, xr.grad) < 2e-3, _rel(xg.grad, xr.grad)
+    # and through the whole audio model: the gradient reaches the waveform on the native path
+    gpu = copy.deepcopy(m).to(dev)
+    xq = (torch.randn(2, 16000, device=dev) * 0.1).requires_grad_(True)
+    gpu(xq).sum().backward()
+    assert xq.grad is not None and float(xq.grad.abs().max()) > 0
