@@ -3,6 +3,12 @@
 Conventions: activations are ``torch.bfloat16`` tensors with logical shape ``[N,C,H,W]`` in
 ``channels_last`` memory format (physical NHWC) or plain ``[M,K]`` matrices; all wrappers launch on the
 current CUDA stream and never synchronise, so everything here is CUDA-graph capturable.
+
+What each group replaces in the reference (all library calls there): cuDNN conv / BN and cuBLAS linear of
+``torchvision.models.resnet18`` and the inline ``Net`` (``notebooks/code/cifar10-distributed-smddp-gpu.py:30-51``), ATen pool / ReLU /
+``CrossEntropyLoss`` / ``optim.SGD`` (``:150-156,162-168``), the torchvision transform pipeline (``:55-62``), and for the MNTD zoo
+``torch.stft`` + mel matmul + ``nn.LSTM`` (``model_lib/audio_rnn_model.py:11,25-36``), the (k x 300) convs of the text CNN
+(``model_lib/rtNLP_cnn_model.py:28-31,49-58``) and the trojan stamping (``model_lib/cifar10_cnn_model.py:77-84``).
 """
 from __future__ import annotations
 
