@@ -18,6 +18,12 @@ x = torch.randint(0, 256, (32, 32, 32, 3), dtype=torch.uint8, generator=g).to(de
 y = torch.randint(0, 10, (32,), generator=g).to(dev)
 mean = torch.tensor((0.4914, 0.4822, 0.4465), device=dev); inv = 1.0 / torch.tensor((0.2023, 0.1994, 0.2010), device=dev)
 model.train()
+# usage: determinism_check.py [model] [deterministic]  -- the second argument turns split-K and the conv-epilogue BN statistics
+# (both meet in fp32 red.adds whose order varies) off, which makes forward and dgrad reproducible bit for bit
+if len(sys.argv) > 2 and sys.argv[2].startswith("det"):
+    from b200ddp.nn import modules as bmod
+    nv.SPLIT_K[0] = False
+    bmod._FUSE_BN_STATS[0] = False
 runs, outs = [], []
 for i in range(4):
     model.zero_grad()
