@@ -70,3 +70,16 @@ def test_reference_cpu_script_runs_unmodified_on_our_ddp(tmp_path):
     assert "Train Epoch: 1" in outs[0] and "Test set: Average loss" in outs[0]
     sd = torch.load(str(tmp_path / "model.pth"), map_location="cpu", weights_only=True)
     assert "conv1.weight" in sd and not any(k.startswith("module.") for k in sd)
+
+
+def test_launcher_takes_the_job_down_when_a_rank_dies_or_hangs():
+    """Fault injection: rank 1 exits with code 3 while rank 0 sits in an all-reduce -> the launcher returns 3
+    and stops rank 0; a rank that hangs trips the launcher's timeout (124).  Nothing keeps running."""
+    import time
+    from b200ddp.utils.launch import launch
+    t0 = time.time()
+    rc = launch(2, ["--fail-rank", "1", "--fail-after", "2", "--exit-code", "3"], module="b200ddp.utils.fault", cpu_hosts=True)
+    assert rc == 3 and time.time() - t0 < 90
+    t0 = time.time()
+    rc = launch(2, ["--fail-rank", "0", "--fail-after", "1", "--hang"], module="b200ddp.utils.fault", cpu_hosts=True, timeout=8.0)
+    assert rc == 124 and time.time() - t0 < 90
