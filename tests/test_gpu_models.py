@@ -92,10 +92,19 @@ def test_model_fwd_bwd_matches_cpu_fp32(name, batch, hw):
     loss_r.backward()
     F.cross_entropy(pure(x), y).backward()
     BF.assume_unit_loss_grad(False)
-    out_g = gpu(x.to(dev))
-    loss_g = BF.cross_entropy(out_g.contiguous(), y.to(dev))
-    loss_g.backward()
-    torch.cuda.synchronize()
+    # reproducible kernels for this comparison (split-K and the conv-epilogue BN statistics meet in fp32 red.adds whose
+    # order varies; resnet18 at init amplifies that, profiles/determinism.md): the bound below is about bf16, not about that
+    from b200ddp.nn import modules as bmod
+    from b200ddp.ops import native as nv
+    saved = (nv.SPLIT_K[0], bmod._FUSE_BN_STATS[0])
+    nv.SPLIT_K[0], bmod._FUSE_BN_STATS[0] = False, False
+    try:
+        out_g = gpu(x.to(dev))
+        loss_g = BF.cross_entropy(out_g.contiguous(), y.to(dev))
+        loss_g.backward()
+        torch.cuda.synchronize()
+    finally:
+        nv.SPLIT_K[0], bmod._FUSE_BN_STATS[0] = saved
     assert _rel(out_g, out_r) < (8e-2 if name == "resnet18" else 2e-2)
     assert abs(float(loss_g.detach()) - float(loss_r.detach())) < 1e-2 * max(1.0, abs(float(loss_r.detach())))
     errs, noise = {}, {}
