@@ -129,6 +129,8 @@ __global__ void __launch_bounds__(T, 1) net_fwd_bwd_kernel(const NetParams p) {
   constexpr int NW = T / 32;
   constexpr int ROWV = F0 / 4;                                // fc1 row length in float4
   int img = 0;
+  pdl_trigger();          // the fc weight-gradient kernel may be scheduled as SMs free up; it waits for this grid in pdl_wait()
+  pdl_wait();
   NET_STAMP(0);
   if (blockIdx.x < p.B) {
     if (p.xu8) prefetch_raw(s.raw[0], p.xu8 + (size_t)blockIdx.x * 3 * H0 * H0, tid);
@@ -583,6 +585,8 @@ __global__ void __launch_bounds__(T, 1) net_fwd_bwd_kernel(const NetParams p) {
 __global__ void __launch_bounds__(416) net_fc_wgrad_kernel(const float* __restrict__ scratch, float* __restrict__ g1,
                                                            float* __restrict__ g2, float* __restrict__ g3, int B, int imgs_per_cta) {
   __shared__ float dh[8][64];
+  pdl_trigger();
+  pdl_wait();
   int bx = blockIdx.x, d_off, a_off, rows, cols;
   float* out;
   if (bx < 15) { d_off = SC_DH1; a_off = SC_P2; rows = F1; cols = F0; out = g1; }
@@ -668,7 +672,7 @@ static int net_launch(NetParams& p, const float* const* params, float* const* gr
   if (grads) {
     const int chunks = batch >= 128 ? 16 : (batch >= 32 ? 8 : 1);
     const int per = (batch + chunks - 1) / chunks;
-    net_fc_wgrad_kernel<<<dim3(28, chunks), 416, 0, s>>>(p.scratch, p.gfw1, p.gfw2, p.gfw3, batch, per);
+    b200_launch(net_fc_wgrad_kernel, dim3(28, chunks), dim3(416), 0, s, (const float*)p.scratch, p.gfw1, p.gfw2, p.gfw3, batch, per);
     B200_CHECK_LAUNCH();
   }
   return 0;
