@@ -241,3 +241,15 @@ def test_conv_bn_pairing_survives_deepcopy_and_keeps_state_dict_keys():
     assert list(c.state_dict().keys()) == list(torchvision.models.resnet18().state_dict().keys())
     x = torch.randn(2, 3, 32, 32)
     assert torch.allclose(m.eval()(x), c.eval()(x))
+
+
+def test_grad_mailbox_protocol():
+    """The bookkeeping behind the fused skip-connection gradient: every consumer but the last deposits, the last one takes the sum."""
+    from b200ddp.ops.functional import GradMailbox
+    mb = GradMailbox(3)
+    assert not mb.arrive()
+    mb.grads.append(torch.ones(4))
+    assert not mb.arrive()
+    mb.grads.append(2 * torch.ones(4))
+    assert mb.arrive()                                   # third consumer is the last
+    assert torch.equal(mb.take(), 3 * torch.ones(4)) and mb.take() is None
