@@ -45,7 +45,7 @@ class Conv2d(nn.Conv2d):
             return BF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0], self.fused_relu)
         x = BF.as_activation(x)
         bn = self._bn_pair
-        if bn is not None and self.training and bn.training and _FUSE_BN_STATS[0]:
+        if bn is not None and self.training and bn.training and _FUSE_BN_STATS[0] and self.out_channels % 8 == 0:
             n, _, h, w = x.shape
             ho = (h + 2 * self.padding[0] - self.kernel_size[0]) // self.stride[0] + 1
             wo = (w + 2 * self.padding[0] - self.kernel_size[1]) // self.stride[0] + 1
