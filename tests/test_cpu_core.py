@@ -253,3 +253,18 @@ def test_grad_mailbox_protocol():
     mb.grads.append(2 * torch.ones(4))
     assert mb.arrive()                                   # third consumer is the last
     assert torch.equal(mb.take(), 3 * torch.ones(4)) and mb.take() is None
+
+
+def test_c_host_example_compiles_links_and_runs(native_lib, tmp_path):
+    """include/b200ddp.h is plain C and the library can be driven without Python."""
+    import shutil
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    libdir = os.path.join(ROOT, "cloud-security-pytorch-sagemaker-distributed-workshop_b200", "_lib")
+    exe = str(tmp_path / "c_host")
+    cmd = ["gcc", "-std=c99", "-Wall", "-Werror", "-O1", "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "examples", "c_host.c"),
+           "-o", exe, "-L", libdir, "-lb200ddp", "-Wl,-rpath," + libdir, "-ldl", "-lpthread", "-lrt"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert out.returncode == 0 and "b200ddp C ABI version" in out.stdout, out.stdout + out.stderr
