@@ -268,3 +268,22 @@ def test_c_host_example_compiles_links_and_runs(native_lib, tmp_path):
     assert res.returncode == 0, res.stderr
     out = subprocess.run([exe], capture_output=True, text=True, timeout=60)
     assert out.returncode == 0 and "b200ddp C ABI version" in out.stdout, out.stdout + out.stderr
+
+
+def test_trainer_saves_full_checkpoint_and_resumes(tmp_path, monkeypatch):
+    """SURVEY 5.4 beyond the reference's save-only model.pth: --save-full-checkpoint then --resume continues at the next epoch
+    with the same weights and optimizer state."""
+    from b200ddp.utils.config import parse_args
+    from b200ddp.workloads.cifar10_train import train
+    for k in ("SM_HOSTS", "SM_CURRENT_HOST", "RANK", "WORLD_SIZE"):
+        monkeypatch.delenv(k, raising=False)
+    common = ["--model-type", "custom", "--synthetic", "--train-size", "256", "--test-size", "64", "--batch-size", "64", "--test-batch-size", "64",
+              "--lr", "0.05", "--momentum", "0.9", "--backend", "gloo", "--model-dir", str(tmp_path), "--log-interval", "1000"]
+    m1 = train(parse_args(common + ["--epochs", "1", "--save-full-checkpoint"]))
+    ck = tmp_path / "checkpoint.pt"
+    assert ck.exists() and (tmp_path / "model.pth").exists()
+    w1 = {k: v.clone() for k, v in m1.state_dict().items()}
+    m2 = train(parse_args(common + ["--epochs", "1", "--resume", str(ck)]))       # start_epoch = 2 > epochs: nothing left to train
+    assert all(torch.equal(w1[k], v) for k, v in m2.state_dict().items())
+    m3 = train(parse_args(common + ["--epochs", "2", "--resume", str(ck)]))       # one more epoch from the restored state
+    assert any(not torch.equal(w1[k], v) for k, v in m3.state_dict().items())
