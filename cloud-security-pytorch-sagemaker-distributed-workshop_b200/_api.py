@@ -7,6 +7,7 @@ from .parallel.process_group import (ReduceOp, all_gather_object, all_reduce, ba
                                      get_device, get_local_rank, get_rank, get_world_size,
                                      init_process_group, is_initialized, max_over_ranks, reduce_op)
 from .parallel.ddp import DistributedDataParallel
+from .ops.functional import get_compute_dtype, set_compute_dtype
 
 __version__ = "0.1.0"
 
@@ -14,5 +15,5 @@ __all__ = [
     "init_process_group", "destroy_process_group", "is_initialized", "get_backend", "get_rank",
     "get_world_size", "get_local_rank", "get_device", "get_comm", "all_reduce", "broadcast", "barrier",
     "all_gather_object", "broadcast_object", "max_over_ranks", "ReduceOp", "reduce_op",
-    "DistributedDataParallel",
+    "DistributedDataParallel", "set_compute_dtype", "get_compute_dtype",
 ]

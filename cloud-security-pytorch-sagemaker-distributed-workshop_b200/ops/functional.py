@@ -27,41 +27,73 @@ def ceil8(v: int) -> int:
     return (v + 7) // 8 * 8
 
 
+# Compute dtype of the native layers: activations (and the weights the tensor cores read) are stored in this type.
+#   torch.float32   fp32 storage, TF32 tensor-core products (tcgen05 kind::tf32), fp32 accumulation -- the precision of the
+#                   reference's own run (fp32 model, cuDNN TF32 convolutions, no autocast: …smddp-gpu.py:145,155-168)
+#   torch.bfloat16  bf16 storage and products (kind::f16), fp32 accumulation, fp32 master weights / gradients
+_ACT_DTYPE = [torch.bfloat16]
+_DTYPE_NAMES = {"fp32": torch.float32, "float32": torch.float32, "tf32": torch.float32,
+                "bf16": torch.bfloat16, "bfloat16": torch.bfloat16}
+
+
+def set_compute_dtype(dtype) -> None:
+    """``'fp32'`` (fp32 storage + TF32 tensor cores) or ``'bf16'``; applies to native layers run after the call."""
+    if isinstance(dtype, str):
+        if dtype.lower() not in _DTYPE_NAMES:
+            raise ValueError("compute dtype must be 'fp32' or 'bf16', got %r" % dtype)
+        dtype = _DTYPE_NAMES[dtype.lower()]
+    if dtype not in (torch.float32, torch.bfloat16):
+        raise ValueError("compute dtype must be torch.float32 or torch.bfloat16, got %s" % dtype)
+    _ACT_DTYPE[0] = dtype
+
+
+def act_dtype() -> torch.dtype:
+    return _ACT_DTYPE[0]
+
+
+def get_compute_dtype() -> str:
+    return "fp32" if _ACT_DTYPE[0] == torch.float32 else "bf16"
+
+
 def as_activation(x: torch.Tensor, channels: Optional[int] = None) -> torch.Tensor:
-    """NCHW (any float dtype) -> bf16 channels-last activation, channel-padded to a multiple of 8."""
+    """NCHW (any float dtype) -> channels-last activation in the compute dtype, channel-padded to a multiple of 8."""
+    dt = _ACT_DTYPE[0]
     if x.dim() == 4:
         c = x.shape[1]
         cp = ceil8(c) if channels is None else channels
         if cp != c:
             x = F.pad(x, (0, 0, 0, 0, 0, cp - c))
-        if x.dtype != torch.bfloat16:
-            x = x.to(torch.bfloat16)
+        if x.dtype != dt:
+            x = x.to(dt)
         return x.contiguous(memory_format=CL)
-    if x.dtype != torch.bfloat16:
-        x = x.to(torch.bfloat16)
+    if x.dtype != dt:
+        x = x.to(dt)
     return x.contiguous()
 
 
 # ------------------------------------------------------------------------------------------------
 # weights: bf16 kernel-layout views ("shadow"), padded when channel counts are not multiples of 8
 # ------------------------------------------------------------------------------------------------
-def conv_weight_shadow(weight: torch.Tensor, cin_pad: int, cout_pad: int) -> torch.Tensor:
-    """[K,C,R,S] fp32 parameter -> bf16 [Kp,R,S,Cp] contiguous (kernel layout)."""
+def conv_weight_shadow(weight: torch.Tensor, cin_pad: int, cout_pad: int, dtype=torch.bfloat16) -> torch.Tensor:
+    """[K,C,R,S] fp32 parameter -> [Kp,R,S,Cp] contiguous in ``dtype`` (kernel layout).  bf16: the shadow copy the fused
+    optimizer maintains; fp32: the master itself (stored channels-last in the DDP arena, so the permute is a view)."""
     K, C, R, S = weight.shape
-    sh = getattr(weight, "_b200_shadow", None)
-    if sh is not None and cin_pad == C and cout_pad == K:
-        return sh                                   # maintained by the fused optimizer, zero cost
+    if dtype == torch.bfloat16:
+        sh = getattr(weight, "_b200_shadow", None)
+        if sh is not None and cin_pad == C and cout_pad == K:
+            return sh                                   # maintained by the fused optimizer, zero cost
     w = weight.detach().permute(0, 2, 3, 1)
     if cin_pad != C or cout_pad != K:
         w = F.pad(w, (0, cin_pad - C, 0, 0, 0, 0, 0, cout_pad - K))
-    return w.to(torch.bfloat16).contiguous()
+    return w.to(dtype).contiguous()
 
 
-def linear_weight_shadow(weight: torch.Tensor, in_pad: int, out_pad: int, nhwc_from=None) -> torch.Tensor:
+def linear_weight_shadow(weight: torch.Tensor, in_pad: int, out_pad: int, nhwc_from=None, dtype=torch.bfloat16) -> torch.Tensor:
     N, K = weight.shape
-    sh = getattr(weight, "_b200_shadow", None)
-    if sh is not None and in_pad == K and out_pad == N and nhwc_from is None:
-        return sh
+    if dtype == torch.bfloat16:
+        sh = getattr(weight, "_b200_shadow", None)
+        if sh is not None and in_pad == K and out_pad == N and nhwc_from is None:
+            return sh
     w = weight.detach()
     if nhwc_from is not None:           # columns are (c,h,w)-ordered in the reference; ours arrive (h,w,cp)
         c, h, ww, cp = nhwc_from
@@ -71,7 +103,7 @@ def linear_weight_shadow(weight: torch.Tensor, in_pad: int, out_pad: int, nhwc_f
         w = w.reshape(N, h * ww * cp)
     if w.shape[1] != in_pad or N != out_pad:
         w = F.pad(w, (0, in_pad - w.shape[1], 0, out_pad - N))
-    return w.to(torch.bfloat16).contiguous()
+    return w.to(dtype).contiguous()
 
 
 def _pad_vec(b: Optional[torch.Tensor], n: int) -> Optional[torch.Tensor]:
@@ -137,7 +169,7 @@ class _Conv2dFn(torch.autograd.Function):
     def forward(ctx, x, weight, bias, stride, pad, relu, bn_sums=None, mailbox=None):
         K, C, R, S = weight.shape
         Cp, Kp = x.shape[1], ceil8(K)
-        w = conv_weight_shadow(weight, Cp, Kp)
+        w = conv_weight_shadow(weight, Cp, Kp, x.dtype)
         b = _pad_vec(bias, Kp)
         y = nv.conv_fwd(x, w, b, stride, pad, relu, bn_sums)
         ctx.save_for_backward(x, w, y if relu else None)
@@ -209,7 +241,7 @@ class _LinearFn(torch.autograd.Function):
     def forward(ctx, x, weight, bias, relu, nhwc_from):
         N, K = weight.shape
         Kp, Np = x.shape[1], ceil8(N)
-        w = linear_weight_shadow(weight, Kp, Np, nhwc_from)
+        w = linear_weight_shadow(weight, Kp, Np, nhwc_from, x.dtype)
         b = _pad_vec(bias, Np)
         y = nv.linear_fwd(x, w, b, relu)
         ctx.save_for_backward(x, w, y if relu else None)
@@ -403,7 +435,7 @@ class _ReluFn(torch.autograd.Function):
 
 
 def relu(x):
-    return F.relu(x) if not x.is_cuda or x.dtype != torch.bfloat16 else _ReluFn.apply(x)
+    return F.relu(x) if not x.is_cuda or x.dtype != _ACT_DTYPE[0] or x.numel() % 8 else _ReluFn.apply(x)
 
 
 def flatten_nhwc(x):

@@ -63,6 +63,15 @@ class _SplitK:
 SPLIT_K = _SplitK()
 
 
+def _fn(name: str, t: torch.Tensor):
+    """The entry point for ``t``'s activation dtype: ``b200_xxx`` takes NHWC bf16, ``b200_xxx_f32`` NHWC fp32."""
+    if t.dtype == torch.bfloat16:
+        return getattr(L.lib(), name)
+    if t.dtype == torch.float32:
+        return getattr(L.lib(), name + "_f32")
+    raise TypeError("b200ddp activations are bfloat16 or float32, got %s" % t.dtype)
+
+
 def _cl_ok(x: torch.Tensor) -> bool:
     return x.dim() == 4 and x.is_contiguous(memory_format=CL)
 
@@ -71,8 +80,8 @@ def to_cl(x: torch.Tensor) -> torch.Tensor:
     return x if _cl_ok(x) else x.contiguous(memory_format=CL)
 
 
-def empty_act(n: int, c: int, h: int, w: int, device) -> torch.Tensor:
-    return torch.empty((n, c, h, w), dtype=torch.bfloat16, device=device, memory_format=CL)
+def empty_act(n: int, c: int, h: int, w: int, device, dtype=torch.bfloat16) -> torch.Tensor:
+    return torch.empty((n, c, h, w), dtype=dtype, device=device, memory_format=CL)
 
 
 # --------------------------------------------------------------------------------------------
@@ -92,17 +101,17 @@ def conv_fwd(x: torch.Tensor, w_krsc: torch.Tensor, bias: Optional[torch.Tensor]
     entry; no bias / ReLU) the epilogue also accumulates the per-channel sum and sum of squares of the output."""
     N, C, H, W = x.shape
     K, R, S, C2 = w_krsc.shape
-    assert C2 == C and _cl_ok(x) and w_krsc.is_contiguous()
+    assert C2 == C and _cl_ok(x) and w_krsc.is_contiguous() and w_krsc.dtype == x.dtype
     Ho, Wo = conv_out_hw(H, W, R, S, stride, pad)
-    y = empty_act(N, K, Ho, Wo, x.device)
+    y = empty_act(N, K, Ho, Wo, x.device, x.dtype)
     g = _geom(N, H, W, C, K, R, S, stride, pad)
     if bn_sums is not None:
         assert bias is None and not relu and bn_sums.numel() >= 2 * K and bn_sums.dtype == torch.float32
-        L.check(L.lib().b200_conv_fwd_stats(L.ptr(x), L.ptr(w_krsc), L.ptr(y), byref(g), L.ptr(bn_sums), L.stream_ptr()),
+        L.check(_fn("b200_conv_fwd_stats", x)(L.ptr(x), L.ptr(w_krsc), L.ptr(y), byref(g), L.ptr(bn_sums), L.stream_ptr()),
                 "conv_fwd_stats")
         return y
-    L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w_krsc), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
-                                  L.stream_ptr()), "conv_fwd")
+    L.check(_fn("b200_conv_fwd", x)(L.ptr(x), L.ptr(w_krsc), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
+                                    L.stream_ptr()), "conv_fwd")
     return y
 
 
@@ -111,15 +120,15 @@ def conv_dgrad(dy: torch.Tensor, w_krsc: torch.Tensor, x_shape, stride: int, pad
     """dx = dgrad(dy, w) (+ residual, a channels-last bf16 tensor of dx's shape, added in the epilogue)."""
     N, C, H, W = x_shape
     K, R, S, _ = w_krsc.shape
-    assert _cl_ok(dy)
-    dx = empty_act(N, C, H, W, dy.device)
+    assert _cl_ok(dy) and w_krsc.dtype == dy.dtype
+    dx = empty_act(N, C, H, W, dy.device, dy.dtype)
     g = _geom(N, H, W, C, K, R, S, stride, pad)
     if residual is not None:
-        assert tuple(residual.shape) == (N, C, H, W) and _cl_ok(residual) and residual.dtype == torch.bfloat16
-        L.check(L.lib().b200_conv_dgrad_add(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.ptr(residual), L.stream_ptr()),
+        assert tuple(residual.shape) == (N, C, H, W) and _cl_ok(residual) and residual.dtype == dy.dtype
+        L.check(_fn("b200_conv_dgrad_add", dy)(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.ptr(residual), L.stream_ptr()),
                 "conv_dgrad_add")
         return dx
-    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.stream_ptr()), "conv_dgrad")
+    L.check(_fn("b200_conv_dgrad", dy)(L.ptr(dy), L.ptr(w_krsc), L.ptr(dx), byref(g), L.stream_ptr()), "conv_dgrad")
     return dx
 
 
@@ -129,9 +138,9 @@ def conv_wgrad_(dw_krsc_f32: torch.Tensor, x: torch.Tensor, dy: torch.Tensor, st
     N, C, H, W = x.shape
     K = dy.shape[1]
     R, S = dw_krsc_f32.shape[1], dw_krsc_f32.shape[2]
-    assert _cl_ok(x) and _cl_ok(dy) and dw_krsc_f32.is_contiguous() and dw_krsc_f32.dtype == torch.float32
+    assert _cl_ok(x) and _cl_ok(dy) and dw_krsc_f32.is_contiguous() and dw_krsc_f32.dtype == torch.float32 and x.dtype == dy.dtype
     g = _geom(N, H, W, C, K, R, S, stride, pad)
-    L.check(L.lib().b200_conv_wgrad(L.ptr(x), L.ptr(dy), L.ptr(dw_krsc_f32), byref(g), c_int(max_splits),
+    L.check(_fn("b200_conv_wgrad", x)(L.ptr(x), L.ptr(dy), L.ptr(dw_krsc_f32), byref(g), c_int(max_splits),
                                     L.stream_ptr()), "conv_wgrad")
 
 
@@ -139,10 +148,10 @@ def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], r
     """x [M,K] bf16, w [N,K] bf16 -> y [M,N] bf16 (a 1x1 convolution on [M,1,1,K])."""
     M, K = x.shape
     N = w.shape[0]
-    assert x.is_contiguous() and w.is_contiguous()
-    y = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    assert x.is_contiguous() and w.is_contiguous() and w.dtype == x.dtype
+    y = torch.empty((M, N), dtype=x.dtype, device=x.device)
     g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
-    L.check(L.lib().b200_conv_fwd(L.ptr(x), L.ptr(w), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
+    L.check(_fn("b200_conv_fwd", x)(L.ptr(x), L.ptr(w), L.ptr(bias), L.ptr(y), byref(g), c_int(int(relu)),
                                   L.stream_ptr()), "linear_fwd")
     return y
 
@@ -150,9 +159,9 @@ def linear_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], r
 def linear_dgrad(dy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     M, N = dy.shape
     K = w.shape[1]
-    dx = torch.empty((M, K), dtype=torch.bfloat16, device=dy.device)
+    dx = torch.empty((M, K), dtype=dy.dtype, device=dy.device)
     g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
-    L.check(L.lib().b200_conv_dgrad(L.ptr(dy), L.ptr(w), L.ptr(dx), byref(g), L.stream_ptr()), "linear_dgrad")
+    L.check(_fn("b200_conv_dgrad", dy)(L.ptr(dy), L.ptr(w), L.ptr(dx), byref(g), L.stream_ptr()), "linear_dgrad")
     return dx
 
 
@@ -161,7 +170,7 @@ def linear_wgrad_(dw_f32: torch.Tensor, x: torch.Tensor, dy: torch.Tensor) -> No
     N = dy.shape[1]
     assert dw_f32.is_contiguous() and dw_f32.dtype == torch.float32
     g = _geom(M, 1, 1, K, N, 1, 1, 1, 0)
-    L.check(L.lib().b200_conv_wgrad(L.ptr(x), L.ptr(dy), L.ptr(dw_f32), byref(g), c_int(0), L.stream_ptr()), "linear_wgrad")
+    L.check(_fn("b200_conv_wgrad", x)(L.ptr(x), L.ptr(dy), L.ptr(dw_f32), byref(g), c_int(0), L.stream_ptr()), "linear_wgrad")
 
 
 # --------------------------------------------------------------------------------------------
@@ -178,7 +187,7 @@ def bn_stats(x: torch.Tensor, gamma, beta, eps: float, momentum: float, running_
     rows, C = _rows_c(x)
     stat = torch.empty((4, C), dtype=torch.float32, device=x.device)
     sc = scratch(x.device)
-    L.check(L.lib().b200_bn_stats(L.ptr(x), c_size_t(rows), c_int(C), L.ptr(gamma), L.ptr(beta), c_float(eps),
+    L.check(_fn("b200_bn_stats", x)(L.ptr(x), c_size_t(rows), c_int(C), L.ptr(gamma), L.ptr(beta), c_float(eps),
                                   c_float(momentum), L.ptr(stat), L.ptr(running_mean), L.ptr(running_var), L.ptr(sc),
                                   c_size_t(sc.numel()), L.stream_ptr()), "bn_stats")
     return stat
@@ -201,7 +210,7 @@ def bn_apply_sums(x, residual, sums, gamma, beta, eps: float, momentum: float, r
     assert sums.numel() >= 2 * C + 1
     stat = torch.empty((4, C), dtype=torch.float32, device=x.device)
     y = torch.empty_like(x)
-    L.check(L.lib().b200_bn_apply_sums(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(sums), L.ptr(gamma),
+    L.check(_fn("b200_bn_apply_sums", x)(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(sums), L.ptr(gamma),
                                        L.ptr(beta), c_float(eps), c_float(momentum), L.ptr(stat), L.ptr(running_mean),
                                        L.ptr(running_var), c_int(int(relu)), L.stream_ptr()), "bn_apply_sums")
     return y, stat
@@ -218,7 +227,7 @@ def bn_eval_prep(gamma, beta, running_mean, running_var, eps: float) -> torch.Te
 def bn_apply(x: torch.Tensor, residual: Optional[torch.Tensor], stat: torch.Tensor, relu: bool) -> torch.Tensor:
     rows, C = _rows_c(x)
     y = torch.empty_like(x)
-    L.check(L.lib().b200_bn_apply(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(stat),
+    L.check(_fn("b200_bn_apply", x)(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(stat),
                                   c_int(int(relu)), L.stream_ptr()), "bn_apply")
     return y
 
@@ -239,7 +248,7 @@ def bn_fwd_fused(x, residual, gamma, beta, eps, momentum, running_mean, running_
     rows, C = _rows_c(x)
     stat = torch.empty((4, C), dtype=torch.float32, device=x.device)
     y = torch.empty_like(x)
-    L.check(L.lib().b200_bn_fwd_fused(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(gamma), L.ptr(beta),
+    L.check(_fn("b200_bn_fwd_fused", x)(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(gamma), L.ptr(beta),
                                       c_float(eps), c_float(momentum), L.ptr(stat), L.ptr(running_mean), L.ptr(running_var),
                                       c_int(int(relu)), L.stream_ptr()), "bn_fwd_fused")
     return y, stat
@@ -249,7 +258,7 @@ def bn_bwd_fused(dy, x, y, stat, relu: bool, want_dres: bool, dgamma=None, dbeta
     rows, C = _rows_c(x)
     dx = torch.empty_like(x)
     dres = torch.empty_like(x) if want_dres else None
-    L.check(L.lib().b200_bn_bwd_fused(L.ptr(dy), L.ptr(x), L.ptr(y), L.ptr(dx), L.ptr(dres), c_size_t(rows), c_int(C),
+    L.check(_fn("b200_bn_bwd_fused", x)(L.ptr(dy), L.ptr(x), L.ptr(y), L.ptr(dx), L.ptr(dres), c_size_t(rows), c_int(C),
                                       L.ptr(stat), c_int(int(relu)), L.ptr(dgamma), L.ptr(dbeta), c_float(beta_accum),
                                       L.stream_ptr()), "bn_bwd_fused")
     return dx, dres
@@ -260,12 +269,12 @@ def bn_bwd(dy, x, y, stat, relu: bool, want_dres: bool, dgamma=None, dbeta=None,
     rows, C = _rows_c(x)
     sums = torch.empty((2, C), dtype=torch.float32, device=x.device)
     sc = scratch(x.device)
-    L.check(L.lib().b200_bn_bwd_reduce(L.ptr(dy), L.ptr(x), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(stat),
+    L.check(_fn("b200_bn_bwd_reduce", x)(L.ptr(dy), L.ptr(x), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(stat),
                                        c_int(int(relu)), L.ptr(sums), L.ptr(dgamma), L.ptr(dbeta), c_float(beta_accum),
                                        L.ptr(sc), c_size_t(sc.numel()), L.stream_ptr()), "bn_bwd_reduce")
     dx = torch.empty_like(x)
     dres = torch.empty_like(x) if want_dres else None
-    L.check(L.lib().b200_bn_bwd_apply(L.ptr(dy), L.ptr(x), L.ptr(y), L.ptr(dx), L.ptr(dres), c_size_t(rows), c_int(C),
+    L.check(_fn("b200_bn_bwd_apply", x)(L.ptr(dy), L.ptr(x), L.ptr(y), L.ptr(dx), L.ptr(dres), c_size_t(rows), c_int(C),
                                       L.ptr(stat), L.ptr(sums), c_int(int(relu)), L.stream_ptr()), "bn_bwd_apply")
     return dx, dres, sums
 
@@ -276,45 +285,45 @@ def bn_bwd(dy, x, y, stat, relu: bool, want_dres: bool, dgamma=None, dbeta=None,
 def maxpool_fwd(x: torch.Tensor, k: int, stride: int, pad: int):
     N, C, H, W = x.shape
     Ho, Wo = conv_out_hw(H, W, k, k, stride, pad)
-    y = empty_act(N, C, Ho, Wo, x.device)
+    y = empty_act(N, C, Ho, Wo, x.device, x.dtype)
     amax = torch.empty((N, Ho, Wo, C), dtype=torch.uint8, device=x.device)
-    L.check(L.lib().b200_maxpool_fwd(L.ptr(x), L.ptr(y), L.ptr(amax), c_int(N), c_int(H), c_int(W), c_int(C), c_int(k),
+    L.check(_fn("b200_maxpool_fwd", x)(L.ptr(x), L.ptr(y), L.ptr(amax), c_int(N), c_int(H), c_int(W), c_int(C), c_int(k),
                                      c_int(stride), c_int(pad), L.stream_ptr()), "maxpool_fwd")
     return y, amax
 
 
 def maxpool_bwd(dy: torch.Tensor, amax: torch.Tensor, x_shape, k: int, stride: int, pad: int) -> torch.Tensor:
     N, C, H, W = x_shape
-    dx = empty_act(N, C, H, W, dy.device)
-    L.check(L.lib().b200_maxpool_bwd(L.ptr(dy), L.ptr(amax), L.ptr(dx), c_int(N), c_int(H), c_int(W), c_int(C), c_int(k),
+    dx = empty_act(N, C, H, W, dy.device, dy.dtype)
+    L.check(_fn("b200_maxpool_bwd", dy)(L.ptr(dy), L.ptr(amax), L.ptr(dx), c_int(N), c_int(H), c_int(W), c_int(C), c_int(k),
                                      c_int(stride), c_int(pad), L.stream_ptr()), "maxpool_bwd")
     return dx
 
 
 def avgpool_fwd(x: torch.Tensor) -> torch.Tensor:
     N, C, H, W = x.shape
-    y = torch.empty((N, C), dtype=torch.bfloat16, device=x.device)
-    L.check(L.lib().b200_avgpool_fwd(L.ptr(x), L.ptr(y), c_int(N), c_int(H * W), c_int(C), L.stream_ptr()), "avgpool_fwd")
+    y = torch.empty((N, C), dtype=x.dtype, device=x.device)
+    L.check(_fn("b200_avgpool_fwd", x)(L.ptr(x), L.ptr(y), c_int(N), c_int(H * W), c_int(C), L.stream_ptr()), "avgpool_fwd")
     return y
 
 
 def avgpool_bwd(dy: torch.Tensor, x_shape) -> torch.Tensor:
     N, C, H, W = x_shape
-    dx = empty_act(N, C, H, W, dy.device)
-    L.check(L.lib().b200_avgpool_bwd(L.ptr(dy), L.ptr(dx), c_int(N), c_int(H * W), c_int(C), L.stream_ptr()), "avgpool_bwd")
+    dx = empty_act(N, C, H, W, dy.device, dy.dtype)
+    L.check(_fn("b200_avgpool_bwd", dy)(L.ptr(dy), L.ptr(dx), c_int(N), c_int(H * W), c_int(C), L.stream_ptr()), "avgpool_bwd")
     return dx
 
 
 def colsum_accum_(out_f32: torch.Tensor, dy: torch.Tensor, c_valid: int) -> None:
     """out[:c_valid] += column sums of dy ([rows, C] bf16 matrix or channels-last activation)."""
     rows, C = _rows_c(dy)
-    L.check(L.lib().b200_colsum_accum(L.ptr(dy), c_size_t(rows), c_int(C), c_int(c_valid), L.ptr(out_f32), L.stream_ptr()),
+    L.check(_fn("b200_colsum_accum", dy)(L.ptr(dy), c_size_t(rows), c_int(C), c_int(c_valid), L.ptr(out_f32), L.stream_ptr()),
             "colsum_accum")
 
 
 def relu_bwd(dy: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
     dx = torch.empty_like(dy)
-    L.check(L.lib().b200_relu_bwd(L.ptr(dy), L.ptr(y), L.ptr(dx), c_size_t(dy.numel()), L.stream_ptr()), "relu_bwd")
+    L.check(_fn("b200_relu_bwd", dy)(L.ptr(dy), L.ptr(y), L.ptr(dx), c_size_t(dy.numel()), L.stream_ptr()), "relu_bwd")
     return dx
 
 
@@ -375,17 +384,22 @@ def cast_bf16_(dst_bf16: torch.Tensor, src_f32: torch.Tensor):
 # data: augmentation, trojan stamping
 # --------------------------------------------------------------------------------------------
 def augment(img_u8: torch.Tensor, offsets: Optional[torch.Tensor], mean: torch.Tensor, inv_std: torch.Tensor,
-            c_out: int = 8, pad: int = 4, nchw_fp32: bool = False) -> torch.Tensor:
-    """uint8 NHWC batch -> normalised activations (NHWC bf16 with zero-padded channels, or NCHW fp32)."""
+            c_out: int = 8, pad: int = 4, nchw_fp32: bool = False, dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    """uint8 NHWC batch -> normalised activations (NHWC with zero-padded channels in the compute dtype -- bf16 or fp32,
+    default ``functional.act_dtype()`` -- or NCHW fp32)."""
     N, H, W, C = img_u8.shape
     assert img_u8.is_contiguous() and img_u8.dtype == torch.uint8
     if nchw_fp32:
         out = torch.empty((N, C, H, W), dtype=torch.float32, device=img_u8.device)
-        c_out = C
+        c_out, layout = C, 1
     else:
-        out = empty_act(N, c_out, H, W, img_u8.device)
+        if dtype is None:
+            from . import functional as _BF
+            dtype = _BF.act_dtype()
+        out = empty_act(N, c_out, H, W, img_u8.device, dtype)
+        layout = 0 if dtype == torch.bfloat16 else 2
     L.check(L.lib().b200_augment(L.ptr(img_u8), L.ptr(offsets), L.ptr(out), c_int(N), c_int(H), c_int(W), c_int(C),
-                                 c_int(c_out), c_int(pad), L.ptr(mean), L.ptr(inv_std), c_int(1 if nchw_fp32 else 0),
+                                 c_int(c_out), c_int(pad), L.ptr(mean), L.ptr(inv_std), c_int(layout),
                                  L.stream_ptr()), "augment")
     return out
 

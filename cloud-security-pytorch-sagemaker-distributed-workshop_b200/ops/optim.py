@@ -50,8 +50,9 @@ class _FusedBase(torch.optim.Optimizer):
                 else:
                     p.grad.zero_()
         for o in self._flat_owners:
-            if not getattr(o, "_grads_zeroed_by_step", False):
+            if getattr(o, "_arena_dirty", True):     # a backward wrote gradients that no fused step has consumed (and zeroed) yet
                 o.flat_grads.zero_()
+                o._arena_dirty = False
 
 
 class SGD(_FusedBase):
@@ -75,7 +76,7 @@ class SGD(_FusedBase):
                 self._momentum_flat[id(o)] = m
             nv.sgd_step(o.flat_params, o.flat_grads, m, o.flat_shadow, g["lr"], g["momentum"], g["dampening"],
                         g["weight_decay"], g["nesterov"], 1.0, True)
-            o._grads_zeroed_by_step = True
+            o._arena_dirty = False                   # the kernel zeroed the arena for the next backward
         if self._inner is not None:
             for k in ("lr", "momentum", "dampening", "weight_decay", "nesterov"):
                 self._inner.param_groups[0][k] = g[k]
@@ -107,7 +108,7 @@ class Adam(_FusedBase):
                 self._state_flat[id(o)] = st
             nv.adam_step(o.flat_params, o.flat_grads, st[0], st[1], o.flat_shadow, g["lr"], g["betas"][0],
                          g["betas"][1], g["eps"], g["weight_decay"], st[2], 1.0, True)
-            o._grads_zeroed_by_step = True
+            o._arena_dirty = False
         if self._inner is not None:
             for k in ("lr", "betas", "eps", "weight_decay"):
                 self._inner.param_groups[0][k] = g[k]

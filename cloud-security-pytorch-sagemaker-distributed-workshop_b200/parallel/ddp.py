@@ -46,7 +46,7 @@ class DistributedDataParallel(nn.Module):
     def __init__(self, module: nn.Module, device_ids=None, output_device=None, dim: int = 0,
                  broadcast_buffers: bool = True, process_group=None, bucket_cap_mb: Optional[float] = None,
                  find_unused_parameters: bool = False, gradient_as_bucket_view: bool = True,
-                 static_graph: bool = True, direct_grad_sink: bool = True, shadow_dtype=torch.bfloat16):
+                 static_graph: bool = True, direct_grad_sink: bool = True, shadow_dtype="auto"):
         super().__init__()
         self.module = module
         self.broadcast_buffers = broadcast_buffers
@@ -91,6 +91,11 @@ class DistributedDataParallel(nn.Module):
         else:
             self.flat_grads = torch.zeros(total, dtype=torch.float32, device=self.device)
         self.flat_shadow = None
+        if shadow_dtype == "auto":
+            # the bf16 shadow feeds the bf16 tensor-core kernels; in fp32 compute mode they read the masters themselves
+            from ..ops.functional import act_dtype
+            shadow_dtype = torch.bfloat16 if act_dtype() == torch.bfloat16 else None
+        self._arena_dirty = False        # gradients have been written since the arena was last zeroed
         if self.device.type == "cuda" and shadow_dtype is not None:
             self.flat_shadow = torch.zeros(total, dtype=shadow_dtype, device=self.device)
 
@@ -142,7 +147,7 @@ class DistributedDataParallel(nn.Module):
             if self.flat_buffers is not None:
                 pg.broadcast(self.flat_buffers, src=0)
             self.refresh_shadow()
-        if self.cfg.debug or True:
+        if self.cfg.debug:
             sizes = ", ".join("%d B (%d tensors)" % (sum(numels[i] for i in b.param_ids) * 4, len(b.param_ids))
                               for b in buckets)
             log.debug("b200ddp.DDP: %d params, %d elements, %d bucket(s): %s", len(self.params),
@@ -189,6 +194,7 @@ class DistributedDataParallel(nn.Module):
     def _on_grad_ready(self, idx: int):
         if not self._callback_queued:
             self._callback_queued = True
+            self._arena_dirty = True
             self.reducer.prepare_for_backward()
             self.reducer.require_sync = self.require_backward_grad_sync
             from torch.autograd import Variable
@@ -207,7 +213,23 @@ class DistributedDataParallel(nn.Module):
             self._accum_count += 1
 
     # ------------------------------------------------------------------ module API
+    def _adopt_dropped_grads(self):
+        """``torch.optim``'s ``zero_grad()`` defaults to ``set_to_none=True``: ``param.grad`` becomes ``None``.  Native layers
+        deposit their weight gradients straight into the arena and never pass through AccumulateGrad, so nothing would
+        re-point ``param.grad`` and a stock optimizer would skip those parameters while the arena kept accumulating.  A
+        dropped gradient means "reset": zero the arena (once) and hand every parameter its arena view back."""
+        dropped = False
+        for p, v in zip(self.params, self._grad_views):
+            if p.grad is None:
+                p.grad = v
+                dropped = True
+        if dropped and self._arena_dirty and self._accum_count == 0:
+            self.flat_grads.zero_()
+            self._arena_dirty = False
+
     def forward(self, *args, **kwargs):
+        if torch.is_grad_enabled():
+            self._adopt_dropped_grads()
         if (self.broadcast_buffers and self.world_size > 1 and self.flat_buffers is not None
                 and self.require_backward_grad_sync and self.training):
             pg.broadcast(self.flat_buffers, src=0)       # KB12: one coalesced broadcast
@@ -225,6 +247,7 @@ class DistributedDataParallel(nn.Module):
     def zero_grad(self, set_to_none: bool = False):   # grads are arena views: zero, never free
         self.flat_grads.zero_()
         self._accum_count = 0
+        self._arena_dirty = False
 
     def refresh_shadow(self):
         """Re-derive the bf16 shadow weights from the fp32 masters (after load_state_dict etc.)."""
@@ -253,4 +276,8 @@ class _GradSink:
         return self.ddp.grad_beta(self.idx)
 
     def done(self):
-        self.ddp._on_grad_ready(self.idx)
+        ddp = self.ddp
+        p = ddp.params[self.idx]
+        if p.grad is None:               # dropped after forward (zero_grad(set_to_none=True) between forward and backward)
+            p.grad = ddp._grad_views[self.idx]
+        ddp._on_grad_ready(self.idx)

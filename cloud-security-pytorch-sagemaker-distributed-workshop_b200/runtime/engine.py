@@ -58,7 +58,10 @@ class TrainStep:
             self.static_loss = torch.zeros((), dtype=torch.float32, device=self.device)
             self._one = torch.ones((), dtype=torch.float32, device=self.device)   # dL/dL, so backward() launches no fill
             self.pin_off = torch.zeros((B, 3), dtype=torch.int32).pin_memory()
+            self._off_ev = None                 # H2D of pin_off still in flight: wait for it before rewriting the buffer
             self.pin_loss = torch.zeros((), dtype=torch.float32).pin_memory()
+            from ..parallel import process_group as _pg
+            self._comm = _pg.get_comm()         # polled after every step: a timed-out collective must not go unnoticed
             BF.assume_unit_loss_grad(True)
             bmod.defer_bn_counters(True)
 
@@ -106,11 +109,33 @@ class TrainStep:
         return loss.detach()
 
     # ------------------------------------------------------------------ graph capture
+    def _training_state(self):
+        """Every tensor a training step mutates besides the gradients: parameters, buffers (BN statistics), optimizer state."""
+        ts = [p.data for p in self.model.parameters()] + [b.data for b in self.model.buffers()]
+        for extra in ("flat_shadow",):
+            t = getattr(self.model, extra, None)
+            if t is not None:
+                ts.append(t)
+        opt = self.optimizer
+        for attr in ("_momentum_flat", "_state_flat"):
+            for v in getattr(opt, attr, {}).values():
+                ts.extend(t for t in (v if isinstance(v, (tuple, list)) else (v,)) if torch.is_tensor(t))
+        for st in getattr(getattr(opt, "_inner", None) or opt, "state", {}).values():
+            ts.extend(t for t in st.values() if torch.is_tensor(t))
+        return ts
+
     def _capture(self):
+        # The warm-up iterations are real optimizer steps on whatever batch sits in the static inputs; they exist to run the
+        # one-time set-up (function attributes, lazily created buffers, optimizer state) outside the capture.  The training
+        # state is snapshotted first and put back afterwards, so a captured run still takes exactly one step per batch
+        # (the reference's loop, …smddp-gpu.py:162-168, never trains a batch twice).
+        before = self._training_state()
+        snap = [t.clone() for t in before]
+        known = {t.data_ptr() for t in before}
         s = torch.cuda.Stream(device=self.device)
         s.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(s):
-            for _ in range(self.warmup_iters):       # also runs one-time setup (func attributes, buffers)
+            for _ in range(self.warmup_iters):
                 loss = self._body(self.static_x, self.static_y, self.static_off)
                 self.static_loss.copy_(loss)
         del loss
@@ -122,7 +147,13 @@ class TrainStep:
             self.static_loss.copy_(loss)
         self._graph = g
         self._pipe_init()
-        self.steps_done += self.warmup_iters       # warm-up iterations were real optimizer steps
+        with torch.no_grad():
+            for t, c in zip(before, snap):
+                t.copy_(c)
+            for t in self._training_state():          # optimizer state created by the warm-up: back to its initial zeros
+                if t.data_ptr() not in known:
+                    t.zero_()
+        torch.cuda.synchronize(self.device)
 
     # ------------------------------------------------------------------ public
     def __call__(self, x_u8: torch.Tensor, y: torch.Tensor, need_loss: bool = False):
@@ -142,10 +173,17 @@ class TrainStep:
             self.static_x.copy_(x_u8, non_blocking=True)
             self.static_y.copy_(y, non_blocking=True)
             if offsets is not None:
+                if self._off_ev is not None:
+                    self._off_ev.synchronize()       # the previous step's H2D of this pinned buffer has executed
                 self.pin_off.copy_(offsets)
                 self.static_off.copy_(self.pin_off, non_blocking=True)
+                if self._off_ev is None:
+                    self._off_ev = torch.cuda.Event()
+                self._off_ev.record()
             self._graph.replay()
             self.steps_done += 1
+            if self._comm is not None:
+                self._comm.check_health()
             if need_loss:
                 self.pin_loss.copy_(self.static_loss, non_blocking=True)
                 torch.cuda.current_stream(self.device).synchronize()
@@ -203,6 +241,8 @@ class TrainStep:
             P["free"][slot].record(cur)
             self._graph.replay()
             self.steps_done += 1
+            if self._comm is not None:
+                self._comm.check_health()            # host-mapped flag: a peer that never arrived raises here, not at the end
             if need_loss:
                 P["pin_loss"][slot].copy_(self.static_loss, non_blocking=True)
             P["ready"][slot].record(cur)

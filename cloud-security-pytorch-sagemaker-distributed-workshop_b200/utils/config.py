@@ -58,7 +58,7 @@ class TrainConfig:
     synthetic: bool = False              # force synthetic CIFAR-10 even when data_dir has files
     train_size: int = 50000
     test_size: int = 10000
-    dtype: str = "bf16"                  # compute dtype of the native kernels ('bf16' | 'fp32')
+    dtype: str = "fp32"                  # compute dtype of the native kernels: 'fp32' (fp32 storage + TF32 tensor cores, the reference's precision) | 'bf16'
     graph: bool = True                   # capture the train step in a CUDA graph
     resume: str = ""                     # optional full checkpoint (model+optimizer+epoch)
     save_full_checkpoint: bool = False
@@ -96,7 +96,7 @@ def add_extension_arguments(parser: argparse.ArgumentParser) -> argparse.Argumen
     parser.add_argument("--synthetic", action="store_true")
     parser.add_argument("--train-size", type=int, default=50000)
     parser.add_argument("--test-size", type=int, default=10000)
-    parser.add_argument("--dtype", type=str, default="bf16", choices=["bf16", "fp32"])
+    parser.add_argument("--dtype", type=str, default="fp32", choices=["bf16", "fp32"])
     parser.add_argument("--no-graph", dest="graph", action="store_false", default=True)
     parser.add_argument("--resume", type=str, default="")
     parser.add_argument("--save-full-checkpoint", action="store_true")

@@ -92,6 +92,7 @@ def train(cfg: TrainConfig):
         bd.init_process_group(backend=backend, rank=rank, world_size=world)
     device = bd.get_device() if bd.is_initialized() else torch.device("cpu")
     torch.manual_seed(cfg.seed)
+    bd.set_compute_dtype(cfg.dtype)      # 'fp32' = the reference's precision (fp32 storage, TF32 tensor cores); 'bf16' optional
 
     divide = cfg.divide_batch if cfg.divide_batch is not None else use_cuda   # …smddp-gpu.py:123-124
     batch_size = max(cfg.batch_size // world, 1) if divide else cfg.batch_size
@@ -125,17 +126,26 @@ def train(cfg: TrainConfig):
         model.train()
         t0 = time.time()
         seen_imgs = 0
-        for batch_idx, (data, target) in enumerate(train_loader, 1):
-            want = batch_idx % cfg.log_interval == 0
-            with tracer.range("train_step"):
-                loss = step(data, target, need_loss=want)
-            seen_imgs += len(data)
-            total_steps += 1
-            if want:
-                logger.info(fmt_train_line(epoch, batch_idx * len(data), len(train_loader.sampler),
-                                           100.0 * batch_idx / len(train_loader), loss))
-            if cfg.max_steps and total_steps >= cfg.max_steps:
-                break
+        # TrainStep.pipeline: batch k+1 is uploaded while step k computes and every loss comes back asynchronously, one
+        # step late -- the same overlapped path bench.py times as "e2e" (without a GPU it degrades to one call per batch)
+        budget = (cfg.max_steps - total_steps) if cfg.max_steps else None
+        sizes = []
+
+        def feed():
+            for i, (data, target) in enumerate(train_loader):
+                if budget is not None and i >= budget:
+                    return
+                sizes.append(len(data))
+                yield data, target
+
+        with tracer.range("train_epoch"):
+            for batch_idx, loss in enumerate(step.pipeline(feed(), need_loss=True), 1):
+                n = sizes[batch_idx - 1]
+                seen_imgs += n
+                total_steps += 1
+                if batch_idx % cfg.log_interval == 0:
+                    logger.info(fmt_train_line(epoch, batch_idx * n, len(train_loader.sampler),
+                                               100.0 * batch_idx / len(train_loader), loss))
         if use_cuda:
             torch.cuda.synchronize(device)
         dt = max(time.time() - t0, 1e-9)
@@ -153,6 +163,13 @@ def train(cfg: TrainConfig):
     step.flush_counters()
     if cfg.trace:
         logger.info("Trace written to %s", tracer.save("%s.rank%d.json" % (cfg.trace, rank)))
+    # A rank whose NVLink collective timed out carries on with partial sums: find out BEFORE the checkpoint is written and
+    # refuse to save a model trained on bad gradients (the reference's launcher is fail-fast the same way: nb2:284)
+    if bd.is_initialized():
+        bd.barrier()
+        comm = bd.get_comm()
+        if comm is not None:
+            comm.check_health()
     logger.info("Saving trained model only on rank 0")
     if rank == 0:
         logger.info("Saving the model.")

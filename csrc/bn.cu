@@ -10,6 +10,7 @@
 // finalises (mean/rstd/scale/shift + running statistics, or dgamma/dbeta).  No atomics on data, no
 // memset, CUDA-graph replayable.
 #include "common.cuh"
+#include "act8.cuh"
 #include <stdlib.h>
 
 namespace {
@@ -19,8 +20,8 @@ constexpr int kVL = 8;                  // 16-byte vector lanes per row  -> 64 c
 constexpr int kRL = kThreads / kVL;     // 32 row lanes
 constexpr int kGroup = kVL * 8;         // 64 channels
 
-__device__ __forceinline__ bf16x8 ld_vec(const __nv_bfloat16* p) { return *reinterpret_cast<const bf16x8*>(p); }
-__device__ __forceinline__ void st_vec(__nv_bfloat16* p, const bf16x8& v) { *reinterpret_cast<bf16x8*>(p) = v; }
+// 8 consecutive channels of one row: one 16-byte vector of bf16, or two of fp32 (act8.cuh); the kernels below are
+// written once over the element type T and instantiated for both activation dtypes.
 
 // reduce acc0/acc1 ([8] per thread) over the 32 row lanes; thread t<128 gets channel (t&63) of array (t>>6)
 __device__ __forceinline__ float cta_reduce_rows(const float* a0, const float* a1, float (*sm)[kRL][kGroup]) {
@@ -81,8 +82,9 @@ __device__ __forceinline__ float sum_partials(const float* partial) {
   return half ? 0.f : t + half_sum[slot];
 }
 
+template <typename T>
 __global__ void __launch_bounds__(kThreads)
-bn_stats_kernel(const __nv_bfloat16* __restrict__ x, size_t rows, int C, const float* __restrict__ gamma,
+bn_stats_kernel(const T* __restrict__ x, size_t rows, int C, const float* __restrict__ gamma,
                 const float* __restrict__ beta, float eps, float momentum, float* __restrict__ stat /*[4][C]*/,
                 float* __restrict__ running_mean, float* __restrict__ running_var, float* __restrict__ partial,
                 unsigned* __restrict__ counters) {
@@ -99,13 +101,13 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, size_t rows, int C, const f
     const size_t step = (size_t)gridDim.x * kRL;
     size_t r = (size_t)blockIdx.x * kRL + rl;
     for (; r + 3 * step < rows; r += 4 * step) {       // 4 independent 16-byte loads in flight per thread
-      bf16x8 v4[4];
+      Act8<T> v4[4];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) v4[u] = ld_vec(x + (r + u * step) * C + c);
+      for (int u = 0; u < 4; ++u) v4[u] = ld_act8(x + (r + u * step) * C + c);
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
         float f[8];
-        bf16x8_to_float(v4[u], f);
+        act8_to_float(v4[u], f);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           s[k] += f[k];
@@ -115,7 +117,7 @@ bn_stats_kernel(const __nv_bfloat16* __restrict__ x, size_t rows, int C, const f
     }
     for (; r < rows; r += step) {
       float f[8];
-      bf16x8_to_float(ld_vec(x + r * C + c), f);
+      act8_to_float(ld_act8(x + r * C + c), f);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         s[k] += f[k];
@@ -194,10 +196,10 @@ __global__ void bn_eval_prep_kernel(const float* gamma, const float* beta, const
   stat[3 * C + ch] = beta[ch] - rm[ch] * sc;
 }
 
-template <bool kRelu, bool kRes>
+template <typename T, bool kRelu, bool kRes>
 __global__ void __launch_bounds__(kThreads)
-bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
-                __nv_bfloat16* __restrict__ y, size_t rows, int C, const float* __restrict__ stat) {
+bn_apply_kernel(const T* __restrict__ x, const T* __restrict__ res,
+                T* __restrict__ y, size_t rows, int C, const float* __restrict__ stat) {
   pdl_trigger();
   pdl_wait();
   const int v = threadIdx.x & (kVL - 1), rl = threadIdx.x >> 3;
@@ -211,9 +213,9 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
   }
   for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
     float f[8];
-    bf16x8_to_float(ld_vec(x + r * C + c), f);
+    act8_to_float(ld_act8(x + r * C + c), f);
     float rr[8];
-    if (kRes) bf16x8_to_float(ld_vec(res + r * C + c), rr);
+    if (kRes) act8_to_float(ld_act8(res + r * C + c), rr);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       float o = fmaf(f[k], sc[k], sh[k]);
@@ -221,17 +223,17 @@ bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
       if (kRelu) o = fmaxf(o, 0.f);
       f[k] = o;
     }
-    st_vec(y + r * C + c, float_to_bf16x8(f));
+    st_act8(y + r * C + c, f);
   }
 }
 
 // bn_apply fed by the per-channel sums of the conv epilogue (b200_conv_fwd_stats): every CTA derives scale/shift for its
 // channel group from the sums, CTA row 0 also writes `stat` (for the backward pass) and the running statistics, and the
 // last CTA to have read the sums (ticket in sums[2C]) zeroes them for the next forward.  One launch, no finalize kernel.
-template <bool kRelu, bool kRes>
+template <typename T, bool kRelu, bool kRes>
 __global__ void __launch_bounds__(kThreads)
-bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
-                     __nv_bfloat16* __restrict__ y, size_t rows, int C, float* __restrict__ sums,
+bn_apply_sums_kernel(const T* __restrict__ x, const T* __restrict__ res,
+                     T* __restrict__ y, size_t rows, int C, float* __restrict__ sums,
                      const float* __restrict__ gamma, const float* __restrict__ beta, float eps, float momentum,
                      float* __restrict__ stat, float* __restrict__ running_mean, float* __restrict__ running_var) {
   pdl_trigger();
@@ -279,9 +281,9 @@ bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
   if (!live) return;
   for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
     float f[8];
-    bf16x8_to_float(ld_vec(x + r * C + c), f);
+    act8_to_float(ld_act8(x + r * C + c), f);
     float rr[8];
-    if (kRes) bf16x8_to_float(ld_vec(res + r * C + c), rr);
+    if (kRes) act8_to_float(ld_act8(res + r * C + c), rr);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       float o = fmaf(f[k], sc[k], sh[k]);
@@ -289,14 +291,14 @@ bn_apply_sums_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* _
       if (kRelu) o = fmaxf(o, 0.f);
       f[k] = o;
     }
-    st_vec(y + r * C + c, float_to_bf16x8(f));
+    st_act8(y + r * C + c, f);
   }
 }
 
-template <bool kRelu>
+template <typename T, bool kRelu>
 __global__ void __launch_bounds__(kThreads)
-bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                     const __nv_bfloat16* __restrict__ y, size_t rows, int C, const float* __restrict__ stat,
+bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                     const T* __restrict__ y, size_t rows, int C, const float* __restrict__ stat,
                      float* __restrict__ sums /*[2][C]*/, float* __restrict__ dgamma, float* __restrict__ dbeta,
                      float beta_accum, float* __restrict__ partial, unsigned* __restrict__ counters) {
   pdl_trigger();
@@ -316,19 +318,19 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     const size_t step = (size_t)gridDim.x * kRL;
     size_t r = (size_t)blockIdx.x * kRL + rl;
     for (; r + step < rows; r += 2 * step) {           // 2 rows x 3 tensors = 6 independent loads in flight
-      bf16x8 gv[2], xr[2], yr[2];
+      Act8<T> gv[2], xr[2], yr[2];
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
-        gv[u] = ld_vec(dy + (r + u * step) * C + c);
-        xr[u] = ld_vec(x + (r + u * step) * C + c);
-        if (kRelu) yr[u] = ld_vec(y + (r + u * step) * C + c);
+        gv[u] = ld_act8(dy + (r + u * step) * C + c);
+        xr[u] = ld_act8(x + (r + u * step) * C + c);
+        if (kRelu) yr[u] = ld_act8(y + (r + u * step) * C + c);
       }
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
         float g[8], xv[8], yv[8];
-        bf16x8_to_float(gv[u], g);
-        bf16x8_to_float(xr[u], xv);
-        if (kRelu) bf16x8_to_float(yr[u], yv);
+        act8_to_float(gv[u], g);
+        act8_to_float(xr[u], xv);
+        if (kRelu) act8_to_float(yr[u], yv);
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
           const float gg = (kRelu && !(yv[k] > 0.f)) ? 0.f : g[k];
@@ -339,9 +341,9 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     }
     for (; r < rows; r += step) {
       float g[8], xv[8], yv[8];
-      bf16x8_to_float(ld_vec(dy + r * C + c), g);
-      bf16x8_to_float(ld_vec(x + r * C + c), xv);
-      if (kRelu) bf16x8_to_float(ld_vec(y + r * C + c), yv);
+      act8_to_float(ld_act8(dy + r * C + c), g);
+      act8_to_float(ld_act8(x + r * C + c), xv);
+      if (kRelu) act8_to_float(ld_act8(y + r * C + c), yv);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const float gg = (kRelu && !(yv[k] > 0.f)) ? 0.f : g[k];
@@ -366,11 +368,11 @@ bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   }
 }
 
-template <bool kRelu, bool kRes>
+template <typename T, bool kRelu, bool kRes>
 __global__ void __launch_bounds__(kThreads)
-bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx,
-                    __nv_bfloat16* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
+bn_bwd_apply_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                    const T* __restrict__ y, T* __restrict__ dx,
+                    T* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
                     const float* __restrict__ sums) {
   pdl_trigger();
   pdl_wait();
@@ -389,17 +391,17 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   }
   for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
     float g[8], xv[8], yv[8];
-    bf16x8_to_float(ld_vec(dy + r * C + c), g);
-    bf16x8_to_float(ld_vec(x + r * C + c), xv);
-    if (kRelu) bf16x8_to_float(ld_vec(y + r * C + c), yv);
+    act8_to_float(ld_act8(dy + r * C + c), g);
+    act8_to_float(ld_act8(x + r * C + c), xv);
+    if (kRelu) act8_to_float(ld_act8(y + r * C + c), yv);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const float gg = (kRelu && !(yv[k] > 0.f)) ? 0.f : g[k];
       g[k] = gg;
       xv[k] = a[k] * (gg - m1[k] - (xv[k] - mean[k]) * rstd[k] * m2[k]);
     }
-    st_vec(dx + r * C + c, float_to_bf16x8(xv));
-    if (kRes) st_vec(dres + r * C + c, float_to_bf16x8(g));
+    st_act8(dx + r * C + c, xv);
+    if (kRes) st_act8(dres + r * C + c, g);
   }
 }
 
@@ -412,7 +414,7 @@ constexpr size_t kSmallRows = 2048;
 // per row each) in registers.  The 16 per-channel sums go warp -> CTA -> cluster (distributed shared memory), after which
 // every CTA applies dx = gamma*rstd*(dy - mean(dy) - xhat*mean(dy*xhat)) to its registers and stores.  One pass over the
 // tensors and one launch instead of the reduce + apply pair (two passes, two launches, a grid-wide ticket).
-constexpr int kClRows = 8;
+template <typename T> constexpr int cl_rows() { return sizeof(T) == 2 ? 8 : 4; }   // 3 tensors x rows x 8 values stay in registers
 constexpr int kClMaxCluster = 8;
 
 __device__ __forceinline__ uint32_t cl_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -429,11 +431,11 @@ __device__ __forceinline__ float cl_ld_peer(const float* local, uint32_t cta) {
   return v;
 }
 
-template <bool kRelu, bool kRes>
+template <typename T, bool kRelu, bool kRes>
 __global__ void __launch_bounds__(kThreads)
-bn_bwd_cluster_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                      const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx,
-                      __nv_bfloat16* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
+bn_bwd_cluster_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                      const T* __restrict__ y, T* __restrict__ dx,
+                      T* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
                       float* __restrict__ dgamma, float* __restrict__ dbeta, float beta_accum, int rows_per_cta, int zc) {
   pdl_trigger();
   pdl_wait();
@@ -451,14 +453,15 @@ bn_bwd_cluster_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16*
     mean[k] = stat[c + k];
     rstd[k] = stat[C + c + k];
   }
-  bf16x8 gv[kClRows], xv[kClRows], yv[kClRows];
+  constexpr int kClRows = cl_rows<T>();
+  Act8<T> gv[kClRows], xv[kClRows], yv[kClRows];
 #pragma unroll
   for (int i = 0; i < kClRows; ++i) {                         // everything this thread will ever read, in flight at once
     const size_t r = r0 + tid + (size_t)i * kThreads;
     if (r < r1) {
-      gv[i] = ld_vec(dy + r * C + c);
-      xv[i] = ld_vec(x + r * C + c);
-      if (kRelu) yv[i] = ld_vec(y + r * C + c);
+      gv[i] = ld_act8(dy + r * C + c);
+      xv[i] = ld_act8(x + r * C + c);
+      if (kRelu) yv[i] = ld_act8(y + r * C + c);
     }
   }
   float s[8], q[8];
@@ -469,9 +472,9 @@ bn_bwd_cluster_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16*
     const size_t r = r0 + tid + (size_t)i * kThreads;
     if (r < r1) {
       float g[8], xf[8], yf[8];
-      bf16x8_to_float(gv[i], g);
-      bf16x8_to_float(xv[i], xf);
-      if (kRelu) bf16x8_to_float(yv[i], yf);
+      act8_to_float(gv[i], g);
+      act8_to_float(xv[i], xf);
+      if (kRelu) act8_to_float(yv[i], yf);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const float gg = (kRelu && !(yf[k] > 0.f)) ? 0.f : g[k];
@@ -522,17 +525,17 @@ bn_bwd_cluster_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16*
     const size_t r = r0 + tid + (size_t)i * kThreads;
     if (r < r1) {
       float g[8], xf[8], yf[8];
-      bf16x8_to_float(gv[i], g);
-      bf16x8_to_float(xv[i], xf);
-      if (kRelu) bf16x8_to_float(yv[i], yf);
+      act8_to_float(gv[i], g);
+      act8_to_float(xv[i], xf);
+      if (kRelu) act8_to_float(yv[i], yf);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const float gg = (kRelu && !(yf[k] > 0.f)) ? 0.f : g[k];
         g[k] = gg;
         xf[k] = a[k] * (gg - m1[k] - (xf[k] - mean[k]) * rstd[k] * m2[k]);
       }
-      st_vec(dx + r * C + c, float_to_bf16x8(xf));
-      if (kRes) st_vec(dres + r * C + c, float_to_bf16x8(g));
+      st_act8(dx + r * C + c, xf);
+      if (kRes) st_act8(dres + r * C + c, g);
     }
   }
   // nobody leaves while a peer may still be reading its tot_s
@@ -540,10 +543,10 @@ bn_bwd_cluster_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16*
   asm volatile("barrier.cluster.wait.aligned;" ::: "memory");
 }
 
-template <bool kRelu, bool kRes>
+template <typename T, bool kRelu, bool kRes>
 __global__ void __launch_bounds__(kThreads)
-bn_fwd_small_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ res,
-                    __nv_bfloat16* __restrict__ y, size_t rows, int C, const float* __restrict__ gamma,
+bn_fwd_small_kernel(const T* __restrict__ x, const T* __restrict__ res,
+                    T* __restrict__ y, size_t rows, int C, const float* __restrict__ gamma,
                     const float* __restrict__ beta, float eps, float momentum, float* __restrict__ stat,
                     float* __restrict__ running_mean, float* __restrict__ running_var) {
   pdl_trigger();
@@ -559,7 +562,7 @@ bn_fwd_small_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
 #pragma unroll 2
     for (size_t r = rl; r < rows; r += kRL) {
       float f[8];
-      bf16x8_to_float(ld_vec(x + r * C + c), f);
+      act8_to_float(ld_act8(x + r * C + c), f);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         s[k] += f[k];
@@ -602,8 +605,8 @@ bn_fwd_small_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
 #pragma unroll 2
   for (size_t r = rl; r < rows; r += kRL) {
     float f[8], rr[8];
-    bf16x8_to_float(ld_vec(x + r * C + c), f);
-    if (kRes) bf16x8_to_float(ld_vec(res + r * C + c), rr);
+    act8_to_float(ld_act8(x + r * C + c), f);
+    if (kRes) act8_to_float(ld_act8(res + r * C + c), rr);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       float o = fmaf(f[k], sc[k], sh[k]);
@@ -611,15 +614,15 @@ bn_fwd_small_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __
       if (kRelu) o = fmaxf(o, 0.f);
       f[k] = o;
     }
-    st_vec(y + r * C + c, float_to_bf16x8(f));
+    st_act8(y + r * C + c, f);
   }
 }
 
-template <bool kRelu, bool kRes>
+template <typename T, bool kRelu, bool kRes>
 __global__ void __launch_bounds__(kThreads)
-bn_bwd_small_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                    const __nv_bfloat16* __restrict__ y, __nv_bfloat16* __restrict__ dx,
-                    __nv_bfloat16* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
+bn_bwd_small_kernel(const T* __restrict__ dy, const T* __restrict__ x,
+                    const T* __restrict__ y, T* __restrict__ dx,
+                    T* __restrict__ dres, size_t rows, int C, const float* __restrict__ stat,
                     float* __restrict__ dgamma, float* __restrict__ dbeta, float beta_accum) {
   pdl_trigger();
   pdl_wait();
@@ -639,9 +642,9 @@ bn_bwd_small_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
 #pragma unroll 2
     for (size_t r = rl; r < rows; r += kRL) {
       float g[8], xv[8], yv[8];
-      bf16x8_to_float(ld_vec(dy + r * C + c), g);
-      bf16x8_to_float(ld_vec(x + r * C + c), xv);
-      if (kRelu) bf16x8_to_float(ld_vec(y + r * C + c), yv);
+      act8_to_float(ld_act8(dy + r * C + c), g);
+      act8_to_float(ld_act8(x + r * C + c), xv);
+      if (kRelu) act8_to_float(ld_act8(y + r * C + c), yv);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         const float gg = (kRelu && !(yv[k] > 0.f)) ? 0.f : g[k];
@@ -672,17 +675,17 @@ bn_bwd_small_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
 #pragma unroll 2
   for (size_t r = rl; r < rows; r += kRL) {
     float g[8], xv[8], yv[8];
-    bf16x8_to_float(ld_vec(dy + r * C + c), g);
-    bf16x8_to_float(ld_vec(x + r * C + c), xv);
-    if (kRelu) bf16x8_to_float(ld_vec(y + r * C + c), yv);
+    act8_to_float(ld_act8(dy + r * C + c), g);
+    act8_to_float(ld_act8(x + r * C + c), xv);
+    if (kRelu) act8_to_float(ld_act8(y + r * C + c), yv);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const float gg = (kRelu && !(yv[k] > 0.f)) ? 0.f : g[k];
       g[k] = gg;
       xv[k] = a[k] * (gg - m1[k] - (xv[k] - mean[k]) * rstd[k] * m2[k]);
     }
-    st_vec(dx + r * C + c, float_to_bf16x8(xv));
-    if (kRes) st_vec(dres + r * C + c, float_to_bf16x8(g));
+    st_act8(dx + r * C + c, xv);
+    if (kRes) st_act8(dres + r * C + c, g);
   }
 }
 
@@ -715,20 +718,29 @@ extern "C" size_t b200_bn_scratch_bytes(size_t rows, int C) {
   return kCounterBytes + (size_t)g.x * g.y * 2 * kGroup * sizeof(float);
 }
 
-extern "C" int b200_bn_stats(const void* x_bf16, size_t rows, int C, const float* gamma, const float* beta, float eps,
-                             float momentum, float* stat, float* running_mean, float* running_var, void* scratch,
-                             size_t scratch_bytes, void* stream) {
-  B200_REQUIRE(x_bf16 && gamma && beta && stat && scratch, "null argument");
+// Every activation-touching entry point exists for both activation dtypes: `name` (NHWC bf16) and `name_f32` (NHWC fp32).
+#define B200_BN_BOTH(name, params, args)                                                  \
+  extern "C" int name params { return name##_impl<__nv_bfloat16> args; }                  \
+  extern "C" int name##_f32 params { return name##_impl<float> args; }
+
+template <typename T>
+static int b200_bn_stats_impl(const void* xv, size_t rows, int C, const float* gamma, const float* beta, float eps,
+                              float momentum, float* stat, float* running_mean, float* running_var, void* scratch,
+                              size_t scratch_bytes, void* stream) {
+  B200_REQUIRE(xv && gamma && beta && stat && scratch, "null argument");
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
   B200_REQUIRE((C + kGroup - 1) / kGroup <= 1024, "too many channel groups");
   B200_REQUIRE(scratch_bytes >= b200_bn_scratch_bytes(rows, C), "scratch too small (b200_bn_scratch_bytes)");
   dim3 g = bn_reduce_grid(rows, C);
-  b200_launch(bn_stats_kernel, dim3(g), dim3(kThreads), 0, (cudaStream_t)stream, 
-      (const __nv_bfloat16*)x_bf16, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var,
-      (float*)((char*)scratch + kCounterBytes), (unsigned*)scratch);
+  b200_launch(bn_stats_kernel<T>, dim3(g), dim3(kThreads), 0, (cudaStream_t)stream, (const T*)xv, rows, C, gamma, beta, eps,
+              momentum, stat, running_mean, running_var, (float*)((char*)scratch + kCounterBytes), (unsigned*)scratch);
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_BN_BOTH(b200_bn_stats,
+             (const void* x, size_t rows, int C, const float* gamma, const float* beta, float eps, float momentum, float* stat,
+              float* running_mean, float* running_var, void* scratch, size_t scratch_bytes, void* stream),
+             (x, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var, scratch, scratch_bytes, stream))
 
 extern "C" int b200_bn_eval_prep(const float* gamma, const float* beta, const float* running_mean,
                                  const float* running_var, float eps, float* stat, int C, void* stream) {
@@ -738,27 +750,32 @@ extern "C" int b200_bn_eval_prep(const float* gamma, const float* beta, const fl
   return 0;
 }
 
-extern "C" int b200_bn_apply(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C,
-                             const float* stat, int relu, void* stream) {
-  B200_REQUIRE(x_bf16 && y_bf16 && stat, "null argument");
+template <typename T>
+static int b200_bn_apply_impl(const void* xv, const void* resv, void* yv, size_t rows, int C, const float* stat, int relu,
+                              void* stream) {
+  B200_REQUIRE(xv && yv && stat, "null argument");
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
   dim3 g = bn_grid(rows, C, 8);
   cudaStream_t s = (cudaStream_t)stream;
-  const __nv_bfloat16 *x = (const __nv_bfloat16*)x_bf16, *r = (const __nv_bfloat16*)residual_bf16;
-  __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
-  if (relu && r) b200_launch(bn_apply_kernel<true, true>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
-  else if (relu) b200_launch(bn_apply_kernel<true, false>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
-  else if (r) b200_launch(bn_apply_kernel<false, true>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
-  else b200_launch(bn_apply_kernel<false, false>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
+  const T *x = (const T*)xv, *r = (const T*)resv;
+  T* y = (T*)yv;
+  if (relu && r) b200_launch(bn_apply_kernel<T, true, true>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
+  else if (relu) b200_launch(bn_apply_kernel<T, true, false>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
+  else if (r) b200_launch(bn_apply_kernel<T, false, true>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
+  else b200_launch(bn_apply_kernel<T, false, false>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, stat);
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_BN_BOTH(b200_bn_apply,
+             (const void* x, const void* residual, void* y, size_t rows, int C, const float* stat, int relu, void* stream),
+             (x, residual, y, rows, C, stat, relu, stream))
 
-extern "C" int b200_bn_bwd_reduce(const void* dy_bf16, const void* x_bf16, const void* y_bf16, size_t rows, int C,
-                                  const float* stat, int relu, float* sums, float* dgamma, float* dbeta,
-                                  float beta_accum, void* scratch, size_t scratch_bytes, void* stream) {
-  B200_REQUIRE(dy_bf16 && x_bf16 && stat && sums && scratch, "null argument");
-  B200_REQUIRE(!relu || y_bf16, "relu mask needs y");
+template <typename T>
+static int b200_bn_bwd_reduce_impl(const void* dyv, const void* xv, const void* yv, size_t rows, int C, const float* stat,
+                                   int relu, float* sums, float* dgamma, float* dbeta, float beta_accum, void* scratch,
+                                   size_t scratch_bytes, void* stream) {
+  B200_REQUIRE(dyv && xv && stat && sums && scratch, "null argument");
+  B200_REQUIRE(!relu || yv, "relu mask needs y");
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
   B200_REQUIRE(scratch_bytes >= b200_bn_scratch_bytes(rows, C), "scratch too small (b200_bn_scratch_bytes)");
   dim3 g = bn_reduce_grid(rows, C);
@@ -766,35 +783,40 @@ extern "C" int b200_bn_bwd_reduce(const void* dy_bf16, const void* x_bf16, const
   float* partial = (float*)((char*)scratch + kCounterBytes);
   unsigned* counters = (unsigned*)scratch;
   if (relu)
-    b200_launch(bn_bwd_reduce_kernel<true>, dim3(g), dim3(kThreads), 0, s, (const __nv_bfloat16*)dy_bf16, (const __nv_bfloat16*)x_bf16,
-                                                     (const __nv_bfloat16*)y_bf16, rows, C, stat, sums, dgamma, dbeta,
-                                                     beta_accum, partial, counters);
+    b200_launch(bn_bwd_reduce_kernel<T, true>, dim3(g), dim3(kThreads), 0, s, (const T*)dyv, (const T*)xv, (const T*)yv, rows, C,
+                stat, sums, dgamma, dbeta, beta_accum, partial, counters);
   else
-    b200_launch(bn_bwd_reduce_kernel<false>, dim3(g), dim3(kThreads), 0, s, (const __nv_bfloat16*)dy_bf16, (const __nv_bfloat16*)x_bf16,
-                                                      (const __nv_bfloat16*)y_bf16, rows, C, stat, sums, dgamma, dbeta,
-                                                      beta_accum, partial, counters);
+    b200_launch(bn_bwd_reduce_kernel<T, false>, dim3(g), dim3(kThreads), 0, s, (const T*)dyv, (const T*)xv, (const T*)yv, rows, C,
+                stat, sums, dgamma, dbeta, beta_accum, partial, counters);
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_BN_BOTH(b200_bn_bwd_reduce,
+             (const void* dy, const void* x, const void* y, size_t rows, int C, const float* stat, int relu, float* sums,
+              float* dgamma, float* dbeta, float beta_accum, void* scratch, size_t scratch_bytes, void* stream),
+             (dy, x, y, rows, C, stat, relu, sums, dgamma, dbeta, beta_accum, scratch, scratch_bytes, stream))
 
-extern "C" int b200_bn_bwd_apply(const void* dy_bf16, const void* x_bf16, const void* y_bf16, void* dx_bf16,
-                                 void* dres_bf16, size_t rows, int C, const float* stat, const float* sums, int relu,
-                                 void* stream) {
-  B200_REQUIRE(dy_bf16 && x_bf16 && dx_bf16 && stat && sums, "null argument");
-  B200_REQUIRE(!relu || y_bf16, "relu mask needs y");
+template <typename T>
+static int b200_bn_bwd_apply_impl(const void* dyv, const void* xv, const void* yv, void* dxv, void* dresv, size_t rows, int C,
+                                  const float* stat, const float* sums, int relu, void* stream) {
+  B200_REQUIRE(dyv && xv && dxv && stat && sums, "null argument");
+  B200_REQUIRE(!relu || yv, "relu mask needs y");
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
   dim3 g = bn_grid(rows, C, 8);
   cudaStream_t s = (cudaStream_t)stream;
-  const __nv_bfloat16 *dy = (const __nv_bfloat16*)dy_bf16, *x = (const __nv_bfloat16*)x_bf16,
-                      *y = (const __nv_bfloat16*)y_bf16;
-  __nv_bfloat16 *dx = (__nv_bfloat16*)dx_bf16, *dr = (__nv_bfloat16*)dres_bf16;
-  if (relu && dr) b200_launch(bn_bwd_apply_kernel<true, true>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
-  else if (relu) b200_launch(bn_bwd_apply_kernel<true, false>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
-  else if (dr) b200_launch(bn_bwd_apply_kernel<false, true>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
-  else b200_launch(bn_bwd_apply_kernel<false, false>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
+  const T *dy = (const T*)dyv, *x = (const T*)xv, *y = (const T*)yv;
+  T *dx = (T*)dxv, *dr = (T*)dresv;
+  if (relu && dr) b200_launch(bn_bwd_apply_kernel<T, true, true>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
+  else if (relu) b200_launch(bn_bwd_apply_kernel<T, true, false>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
+  else if (dr) b200_launch(bn_bwd_apply_kernel<T, false, true>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
+  else b200_launch(bn_bwd_apply_kernel<T, false, false>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, sums);
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_BN_BOTH(b200_bn_bwd_apply,
+             (const void* dy, const void* x, const void* y, void* dx, void* dres, size_t rows, int C, const float* stat,
+              const float* sums, int relu, void* stream),
+             (dy, x, y, dx, dres, rows, C, stat, sums, relu, stream))
 
 // ------------------------------------------------------------------------------------------------
 // b200_bn_stats_noalloc — the same statistics pass for callers that cannot allocate device memory.
@@ -804,15 +826,18 @@ extern "C" int b200_bn_bwd_apply(const void* dy_bf16, const void* x_bf16, const 
 // implicit device-wide synchronisation is not acceptable, and plain-C / non-torch runtimes binding this
 // library through the C ABI, which have no caching allocator to borrow a scratch buffer from.  For them the
 // reduction scratch (ticket counters + per-CTA partial sums) lives in the fixed array below instead of a
-// caller-provided buffer.  Inputs and outputs are still passed by the caller.
+// caller-provided buffer.  Inputs and outputs are still passed by the caller (bf16 activations).
 //
 // Limits and rules
 //   * The array is B200_BN_NOALLOC_SCRATCH_BYTES (1 MiB) per GPU; every GPU that loads this library holds it
 //     until the process exits.  A problem whose b200_bn_scratch_bytes(rows, C) exceeds it is rejected with an
-//     error (rc < 0, text in b200_last_error()); 1 MiB covers up to ~2000 (row-block x channel-group) tiles,
-//     e.g. C <= 1024 at any row count.
+//     error (rc < 0, text in b200_last_error()).  The scratch is 4 KiB of counters plus 512 B per (row-block x
+//     channel-group) tile, with one tile per 256 rows up to 128 row blocks and one channel group per 64
+//     channels: 1 MiB holds 2040 tiles, i.e. C <= 960 at any row count, and C = 1024 up to 32,767 rows.
 //   * The first call on each device resolves the array's device address (cudaGetSymbolAddress with that device
-//     current) and caches it.  Make that first call outside any stream capture.
+//     current) and caches it.  Make that first call outside any stream capture.  The cache is filled without a
+//     lock: first calls on one device from several host threads at once are safe (they all store the same
+//     address) but each of them repeats the lookup.
 //   * This entry point calls no cudaMalloc/cudaFree and no allocating library routine.
 //   * All calls on a device share the one array and it keeps whatever the previous call left.  The ticket
 //     counters must start at zero, so every call clears them on `stream` before the kernel.  Two calls whose
@@ -855,9 +880,8 @@ extern "C" int b200_bn_stats_noalloc(const void* x_bf16, size_t rows, int C, con
   // the tickets must be zero when the kernel starts; whatever an earlier (possibly aborted) call left goes
   B200_CHECK_CUDA(cudaMemsetAsync(scratch, 0, kCounterBytes, s));
   dim3 g = bn_reduce_grid(rows, C);
-  b200_launch(bn_stats_kernel, dim3(g), dim3(kThreads), 0, s, (const __nv_bfloat16*)x_bf16, rows, C, gamma, beta, eps, momentum, stat,
-                                         running_mean, running_var, (float*)(scratch + kCounterBytes),
-                                         (unsigned*)scratch);
+  b200_launch(bn_stats_kernel<__nv_bfloat16>, dim3(g), dim3(kThreads), 0, s, (const __nv_bfloat16*)x_bf16, rows, C, gamma, beta, eps,
+              momentum, stat, running_mean, running_var, (float*)(scratch + kCounterBytes), (unsigned*)scratch);
   B200_CHECK_LAUNCH();
   return 0;
 }
@@ -865,21 +889,23 @@ extern "C" int b200_bn_stats_noalloc(const void* x_bf16, size_t rows, int C, con
 extern "C" size_t b200_bn_small_rows(void) { return kSmallRows; }
 
 // rows above which b200_bn_bwd_fused switches from the one-CTA-per-64-channels kernel to the cluster kernel
-// (B200DDP_BN_CLUSTER_MIN_ROWS, default 256); the cluster kernel takes up to 8 rows x 256 threads x 8 CTAs.
+// (B200DDP_BN_CLUSTER_MIN_ROWS, default 256); the cluster kernel takes up to 8 (bf16) / 4 (fp32) rows x 256 threads x 8 CTAs.
 static const size_t g_bn_cluster_min_rows = []() { const char* e = getenv("B200DDP_BN_CLUSTER_MIN_ROWS"); return (size_t)(e ? atoll(e) : 256); }();
-extern "C" size_t b200_bn_bwd_fused_max_rows(void) { return (size_t)kClRows * kThreads * kClMaxCluster; }
+extern "C" size_t b200_bn_bwd_fused_max_rows(void) { return (size_t)cl_rows<__nv_bfloat16>() * kThreads * kClMaxCluster; }
+extern "C" size_t b200_bn_bwd_fused_max_rows_f32(void) { return (size_t)cl_rows<float>() * kThreads * kClMaxCluster; }
 
-extern "C" int b200_bn_fwd_fused(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C,
-                                 const float* gamma, const float* beta, float eps, float momentum, float* stat,
-                                 float* running_mean, float* running_var, int relu, void* stream) {
-  B200_REQUIRE(x_bf16 && y_bf16 && gamma && beta && stat, "null argument");
+template <typename T>
+static int b200_bn_fwd_fused_impl(const void* xv, const void* resv, void* yv, size_t rows, int C, const float* gamma,
+                                  const float* beta, float eps, float momentum, float* stat, float* running_mean,
+                                  float* running_var, int relu, void* stream) {
+  B200_REQUIRE(xv && yv && gamma && beta && stat, "null argument");
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
   B200_REQUIRE(rows <= kSmallRows, "fused BN forward handles at most b200_bn_small_rows() rows; use bn_stats + bn_apply");
   dim3 g(1, (C + kGroup - 1) / kGroup, 1);
   cudaStream_t s = (cudaStream_t)stream;
-  const __nv_bfloat16 *x = (const __nv_bfloat16*)x_bf16, *r = (const __nv_bfloat16*)residual_bf16;
-  __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
-#define B200_BNF(R, S) b200_launch(bn_fwd_small_kernel<R, S>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var)
+  const T *x = (const T*)xv, *r = (const T*)resv;
+  T* y = (T*)yv;
+#define B200_BNF(R, S) b200_launch(bn_fwd_small_kernel<T, R, S>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var)
   if (relu && r) B200_BNF(true, true);
   else if (relu) B200_BNF(true, false);
   else if (r) B200_BNF(false, true);
@@ -888,17 +914,22 @@ extern "C" int b200_bn_fwd_fused(const void* x_bf16, const void* residual_bf16, 
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_BN_BOTH(b200_bn_fwd_fused,
+             (const void* x, const void* residual, void* y, size_t rows, int C, const float* gamma, const float* beta, float eps,
+              float momentum, float* stat, float* running_mean, float* running_var, int relu, void* stream),
+             (x, residual, y, rows, C, gamma, beta, eps, momentum, stat, running_mean, running_var, relu, stream))
 
-extern "C" int b200_bn_bwd_fused(const void* dy_bf16, const void* x_bf16, const void* y_bf16, void* dx_bf16,
-                                 void* dres_bf16, size_t rows, int C, const float* stat, int relu, float* dgamma,
-                                 float* dbeta, float beta_accum, void* stream) {
-  B200_REQUIRE(dy_bf16 && x_bf16 && dx_bf16 && stat, "null argument");
-  B200_REQUIRE(!relu || y_bf16, "relu mask needs y");
+template <typename T>
+static int b200_bn_bwd_fused_impl(const void* dyv, const void* xv, const void* yv, void* dxv, void* dresv, size_t rows, int C,
+                                  const float* stat, int relu, float* dgamma, float* dbeta, float beta_accum, void* stream) {
+  B200_REQUIRE(dyv && xv && dxv && stat, "null argument");
+  B200_REQUIRE(!relu || yv, "relu mask needs y");
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
-  B200_REQUIRE(rows <= b200_bn_bwd_fused_max_rows(), "fused BN backward handles at most b200_bn_bwd_fused_max_rows() rows");
+  constexpr int kClRows = cl_rows<T>();
+  B200_REQUIRE(rows <= (size_t)kClRows * kThreads * kClMaxCluster, "fused BN backward handles at most b200_bn_bwd_fused_max_rows() rows");
   cudaStream_t s = (cudaStream_t)stream;
-  const __nv_bfloat16 *dy = (const __nv_bfloat16*)dy_bf16, *x = (const __nv_bfloat16*)x_bf16, *y = (const __nv_bfloat16*)y_bf16;
-  __nv_bfloat16 *dx = (__nv_bfloat16*)dx_bf16, *dr = (__nv_bfloat16*)dres_bf16;
+  const T *dy = (const T*)dyv, *x = (const T*)xv, *y = (const T*)yv;
+  T *dx = (T*)dxv, *dr = (T*)dresv;
   if (rows > g_bn_cluster_min_rows || rows > kSmallRows) {
     // cluster kernel: 8 channels per cluster; grow the cluster until ~96 CTAs are in flight or a thread has one row
     const int per_cta_max = kClRows * kThreads;
@@ -920,7 +951,7 @@ extern "C" int b200_bn_bwd_fused(const void* dy_bf16, const void* x_bf16, const 
     attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = b200_pdl_enabled() ? 2 : 1;
-#define B200_BNC(R, S) B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, bn_bwd_cluster_kernel<R, S>, dy, x, y, dx, dr, rows, C, stat, dgamma, dbeta, beta_accum, rows_per_cta, zc))
+#define B200_BNC(R, S) B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, bn_bwd_cluster_kernel<T, R, S>, dy, x, y, dx, dr, rows, C, stat, dgamma, dbeta, beta_accum, rows_per_cta, zc))
     if (relu && dr) B200_BNC(true, true);
     else if (relu) B200_BNC(true, false);
     else if (dr) B200_BNC(false, true);
@@ -929,7 +960,7 @@ extern "C" int b200_bn_bwd_fused(const void* dy_bf16, const void* x_bf16, const 
     return 0;
   }
   dim3 g(1, (C + kGroup - 1) / kGroup, 1);
-#define B200_BNB(R, S) b200_launch(bn_bwd_small_kernel<R, S>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, dgamma, dbeta, beta_accum)
+#define B200_BNB(R, S) b200_launch(bn_bwd_small_kernel<T, R, S>, dim3(g), dim3(kThreads), 0, s, dy, x, y, dx, dr, rows, C, stat, dgamma, dbeta, beta_accum)
   if (relu && dr) B200_BNB(true, true);
   else if (relu) B200_BNB(true, false);
   else if (dr) B200_BNB(false, true);
@@ -938,6 +969,10 @@ extern "C" int b200_bn_bwd_fused(const void* dy_bf16, const void* x_bf16, const 
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_BN_BOTH(b200_bn_bwd_fused,
+             (const void* dy, const void* x, const void* y, void* dx, void* dres, size_t rows, int C, const float* stat, int relu,
+              float* dgamma, float* dbeta, float beta_accum, void* stream),
+             (dy, x, y, dx, dres, rows, C, stat, relu, dgamma, dbeta, beta_accum, stream))
 
 // Training-mode BN statistics from per-channel sums that the conv epilogue accumulated (b200_conv_fwd_stats): writes
 // stat[4][C] = mean, rstd, gamma*rstd, beta - mean*gamma*rstd, updates the running statistics, zeroes `sums`.
@@ -952,16 +987,17 @@ extern "C" int b200_bn_finalize(float* sums, size_t rows, int C, const float* ga
 
 // BN(+residual)(+ReLU) forward in ONE launch from the conv epilogue's sums: sums[0..C) sum, [C..2C) sum of squares,
 // sums[2C] a ticket word; all zero on entry and zero again afterwards.  Also writes stat[4][C] and the running statistics.
-extern "C" int b200_bn_apply_sums(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C, float* sums,
-                                  const float* gamma, const float* beta, float eps, float momentum, float* stat,
-                                  float* running_mean, float* running_var, int relu, void* stream) {
-  B200_REQUIRE(x_bf16 && y_bf16 && sums && gamma && beta && stat, "null argument");
+template <typename T>
+static int b200_bn_apply_sums_impl(const void* xv, const void* resv, void* yv, size_t rows, int C, float* sums, const float* gamma,
+                                   const float* beta, float eps, float momentum, float* stat, float* running_mean,
+                                   float* running_var, int relu, void* stream) {
+  B200_REQUIRE(xv && yv && sums && gamma && beta && stat, "null argument");
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
   dim3 g = bn_grid(rows, C, 8);
   cudaStream_t s = (cudaStream_t)stream;
-  const __nv_bfloat16 *x = (const __nv_bfloat16*)x_bf16, *r = (const __nv_bfloat16*)residual_bf16;
-  __nv_bfloat16* y = (__nv_bfloat16*)y_bf16;
-#define B200_BNAS(R, S) b200_launch(bn_apply_sums_kernel<R, S>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, sums, gamma, beta, eps, momentum, stat, running_mean, running_var)
+  const T *x = (const T*)xv, *r = (const T*)resv;
+  T* y = (T*)yv;
+#define B200_BNAS(R, S) b200_launch(bn_apply_sums_kernel<T, R, S>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, sums, gamma, beta, eps, momentum, stat, running_mean, running_var)
   if (relu && r) B200_BNAS(true, true);
   else if (relu) B200_BNAS(true, false);
   else if (r) B200_BNAS(false, true);
@@ -970,3 +1006,7 @@ extern "C" int b200_bn_apply_sums(const void* x_bf16, const void* residual_bf16,
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_BN_BOTH(b200_bn_apply_sums,
+             (const void* x, const void* residual, void* y, size_t rows, int C, float* sums, const float* gamma, const float* beta,
+              float eps, float momentum, float* stat, float* running_mean, float* running_var, int relu, void* stream),
+             (x, residual, y, rows, C, sums, gamma, beta, eps, momentum, stat, running_mean, running_var, relu, stream))

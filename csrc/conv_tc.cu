@@ -5,8 +5,15 @@
 // (torchvision resnet18 under notebooks/code/cifar10-distributed-smddp-gpu.py:32,165-167; MNTD models
 // notebooks/code/model_lib/cifar10_cnn_model.py:11-18, mnist_cnn_model.py:11-15).
 //
-// One kernel template, three modes.  Activations are NHWC bf16, weights are [Cout][R][S][Cin] bf16 (the
-// channels-last physical layout of the flat parameter arena), accumulation is fp32 in TMEM.
+// One kernel template, three modes, two operand types.  Activations are NHWC, weights are [Cout][R][S][Cin] (the
+// channels-last physical layout of the flat parameter arena), accumulation is fp32 in TMEM.  T = __nv_bfloat16 runs
+// tcgen05.mma kind::f16 (K = 16 per instruction); T = float keeps activations, weights and gradients in fp32 storage and
+// runs kind::tf32 (K = 8 per instruction: the tensor core reads the top 19 bits of every fp32 operand) -- the precision
+// of the reference's own run, which trains fp32 with cuDNN's TF32 convolutions and no autocast
+// (notebooks/code/cifar10-distributed-smddp-gpu.py:145,155-168).  A 128-byte swizzle row holds 64 bf16 or 32 fp32, so the
+// shared-memory tiles, the ring and the descriptors' byte arithmetic are the same for both; what changes is elements per
+// 16-byte chunk (8 / 4), k-blocks per filter tap, and the MN-major (transposed) operand layout, which for 32-bit elements
+// must be the "128B swizzle with 32-byte atomicity" form (4-row atoms, 32-byte units XORed with the row index).
 //
 //   FWD    D[m=(n,ho,wo)][co]   = sum_{r,s,ci} X[n, ho*st-p+r, wo*st-p+s, ci] * W[co][r][s][ci]
 //          A: gathered K-major,  B: weight rows K-major.            D -> bf16 (+bias, ReLU)
@@ -36,6 +43,7 @@
 #include <algorithm>
 
 #include "tc_ptx.cuh"
+#include "act8.cuh"
 
 using namespace b200tc;
 
@@ -43,7 +51,11 @@ namespace {
 
 constexpr int MODE_FWD = 0, MODE_DGRAD = 1, MODE_WGRAD = 2;
 constexpr int BM = 128;
-constexpr int BK = 64;                 // bf16 elements per k-block = one 128-byte swizzle row
+// per operand type: bytes per element, elements per 16-byte chunk, K elements per k-block (= one 128-byte swizzle row),
+// K per tcgen05.mma, and the A/B format code of the instruction descriptor (1 = BF16, 2 = TF32)
+template <typename T> struct El;
+template <> struct El<__nv_bfloat16> { static constexpr int ES = 2, EPC = 8, BK = 64, UK = 16; static constexpr uint32_t FMT = 1; };
+template <> struct El<float> { static constexpr int ES = 4, EPC = 4, BK = 32, UK = 8; static constexpr uint32_t FMT = 2; };
 // Operand ring depth ST (template parameter): 6 stages / 1 CTA per SM for the latency-bound small problems, 3 stages /
 // 2 CTAs per SM for grids of many tiles (one tile's load latency and epilogue hide behind the other CTA's MMAs).
 constexpr int lag_for(int st) { return st >= 6 ? 4 : 2; }   // cp.async groups kept in flight behind the newest one
@@ -53,12 +65,12 @@ long long* g_prof = nullptr;           // b200_conv_set_profile_buffer
 bool g_split_k = true;                 // b200_conv_set_split_k(0) pins FWD/DGRAD to one CTA per tile (reproducibility checks)
 
 struct ConvParams {
-  const __nv_bfloat16* x;    // image-side tensor (FWD/WGRAD: input, DGRAD: unused)
-  const __nv_bfloat16* w;    // [Cout][R][S][Cin]
-  const __nv_bfloat16* dy;   // output-side tensor (DGRAD/WGRAD)
-  void* out;                 // FWD: y bf16 [M][Cout]; DGRAD: dx bf16 [M][Cin]; WGRAD: dw fp32 [Cout][R*S*Cin]
+  const void* x;             // image-side tensor (FWD/WGRAD: input, DGRAD: unused); element type T of the kernel
+  const void* w;             // [Cout][R][S][Cin]
+  const void* dy;            // output-side tensor (DGRAD/WGRAD)
+  void* out;                 // FWD: y T [M][Cout]; DGRAD: dx T [M][Cin]; WGRAD: dw fp32 [Cout][R*S*Cin]
   const float* bias;         // FWD only, may be null
-  const __nv_bfloat16* residual;   // DGRAD only, may be null: added to the output (the other gradient of a forked tensor)
+  const void* residual;      // DGRAD only, may be null: added to the output (the other gradient of a forked tensor)
   float* bn_sums;            // FWD only, may be null: per-channel sum [gemm_n] and sum of squares [gemm_n] of the output
   int N, H, W, C;            // input geometry (C = Cin)
   int Kc, R, S, stride, pad; // Kc = Cout
@@ -75,12 +87,12 @@ struct ConvParams {
   FastDiv div_c, div_s, div_kc, div_wo, div_ho, div_w, div_h, div_cpt;
 };
 
-template <int MODE, int BN, int ST = 6>
+template <typename T, int MODE, int BN, int ST = 6>
 struct Cfg {
   static constexpr bool A_MN = (MODE == MODE_WGRAD);
   static constexpr bool B_MN = (MODE != MODE_FWD);
-  static constexpr int A_BYTES = BM * BK * 2;          // 16 KiB either way
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int A_BYTES = BM * 128;             // BM rows (K-major) or BK k-rows x BM/(128/ES) groups (MN-major) of 128 B
+  static constexpr int B_BYTES = BN * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int SMEM_BYTES = ST * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/ + 2048 /*row info*/;
 };
@@ -131,14 +143,14 @@ __device__ __forceinline__ void bn_stats_accumulate(const ConvParams& p, uint32_
 // Write NCOLS accumulator columns [nn0, nn0+NCOLS) of GEMM row m, 8 columns (one 16-byte bf16 vector) at a
 // time; gemm_n is a multiple of 8 in every mode.  FWD: +bias, ReLU, bf16.  DGRAD: (+residual) bf16.  WGRAD: fp32 red.add
 // into the gradient arena.  Kept small on purpose: a tile runs this code once, so its size is fetch latency.
-template <int MODE, int NCOLS>
+template <typename T, int MODE, int NCOLS>
 __device__ __forceinline__ void epilogue_store(const ConvParams& p, uint32_t m, uint32_t nn0, float* f) {
   if (m >= p.gemm_m) return;
-  bf16x8 resv[NCOLS / 8];
+  Act8<T> resv[NCOLS / 8];
   if (MODE == MODE_DGRAD && p.residual != nullptr) {        // all of this row's residual vectors in flight at once
 #pragma unroll
     for (int q = 0; q < NCOLS / 8; ++q)
-      if (nn0 + 8 * q < p.gemm_n) resv[q] = *reinterpret_cast<const bf16x8*>(p.residual + (size_t)m * p.gemm_n + nn0 + 8 * q);
+      if (nn0 + 8 * q < p.gemm_n) resv[q] = ld_act8(reinterpret_cast<const T*>(p.residual) + (size_t)m * p.gemm_n + nn0 + 8 * q);
   }
 #pragma unroll
   for (int q = 0; q < NCOLS / 8; ++q) {
@@ -164,21 +176,25 @@ __device__ __forceinline__ void epilogue_store(const ConvParams& p, uint32_t m, 
       }
       if (MODE == MODE_DGRAD && p.residual != nullptr) {
         float r[8];
-        bf16x8_to_float(resv[q], r);
+        act8_to_float(resv[q], r);
 #pragma unroll
         for (int k = 0; k < 8; ++k) v[k] += r[k];
       }
-      *reinterpret_cast<bf16x8*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)m * p.gemm_n + nn) = float_to_bf16x8(v);
+      st_act8(reinterpret_cast<T*>(p.out) + (size_t)m * p.gemm_n + nn, v);
     }
   }
 }
 
-template <int MODE, int BN, int ZC, int ST>
+template <typename T, int MODE, int BN, int ZC, int ST>
 __global__ void __launch_bounds__(THREADS, (ST <= 3 ? 2 : 1))
 conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUtensorMap tmA,
                const __grid_constant__ CUtensorMap tmB) {
-  using C = Cfg<MODE, BN, ST>;
+  using C = Cfg<T, MODE, BN, ST>;
   constexpr int STAGES = ST, LAG = lag_for(ST);
+  constexpr int BK = El<T>::BK, EPC = El<T>::EPC;
+  const T* const px = reinterpret_cast<const T*>(p.x);
+  const T* const pw = reinterpret_cast<const T*>(p.w);
+  const T* const pdy = reinterpret_cast<const T*>(p.dy);
   pdl_trigger();                  // the next kernel of the stream may be scheduled now; it waits for us in its own pdl_wait()
   const uint32_t m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
   if (MODE == MODE_WGRAD && p.cpt != 0) {
@@ -196,7 +212,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
-  const __nv_bfloat16** s_rowbase = reinterpret_cast<const __nv_bfloat16**>(smem + STAGES * C::STAGE_BYTES + 256);
+  const T** s_rowbase = reinterpret_cast<const T**>(smem + STAGES * C::STAGE_BYTES + 256);
   unsigned long long* s_rowmask = reinterpret_cast<unsigned long long*>(smem + STAGES * C::STAGE_BYTES + 256 + 1024);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -231,20 +247,20 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
       // =============================== PRODUCERS (cp.async gather) ===============================
       const uint32_t smem_base = smem_u32(smem);
       // K-major A (FWD/DGRAD): thread owns chunk column tid&7 of rows (tid>>3) + 16*i, i<8
-      // MN-major A (WGRAD): 16 chunks per K row: column tid&15, rows (tid>>4) + 8*i, i<8
+      // MN-major A (WGRAD): BM/EPC chunks per K row (16 bf16 / 32 fp32): column tid % CPRA, rows tid / CPRA + RPPA*i, i<8
       // Per row: a base pointer and a bit mask of the filter taps that land on a real pixel, computed once per
       // tile by ONE thread per row (through shared memory).  In the K loop an A chunk is then
       // `rowbase[i] + tap_offset + channel` guarded by one bit test.
       //   FWD   base = &x[n, ho*st-pad, wo*st-pad, 0],   tap (r,s) adds  (r*W + s)*C
       //   DGRAD base = &dy[n, (h+pad)>>sh, (w+pad)>>sh, 0], tap (r,s) subtracts ((r>>sh)*Wo + (s>>sh))*Kc, sh = stride==2;
       //         a tap is live when (h+pad-r), (w+pad-s) are multiples of the stride and inside the output map.
-      const __nv_bfloat16* rowbase[8];
+      const T* rowbase[8];
       unsigned long long rowmask[8];
       if (MODE != MODE_WGRAD && !p.a_tma) {
         const int sh = (p.stride == 2) ? 1 : 0;
         {
           const uint32_t m = m0 + tid;                      // tid < 128: this thread's row
-          const __nv_bfloat16* base = (MODE == MODE_FWD) ? p.x : p.dy;
+          const T* base = (MODE == MODE_FWD) ? px : pdy;
           unsigned long long mask = 0ull;
           if (m < p.gemm_m) {
             int h0, w0, hlim, wlim;
@@ -252,12 +268,12 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
               const uint32_t t = fdiv(m, p.div_wo), wo = m - t * p.Wo;
               const uint32_t n = fdiv(t, p.div_ho), ho = t - n * p.Ho;
               h0 = (int)ho * p.stride - p.pad; w0 = (int)wo * p.stride - p.pad; hlim = p.H; wlim = p.W;
-              base = p.x + (((long long)n * p.H + h0) * p.W + w0) * p.C;
+              base = px + (((long long)n * p.H + h0) * p.W + w0) * p.C;
             } else {
               const uint32_t t = fdiv(m, p.div_w), w = m - t * p.W;
               const uint32_t n = fdiv(t, p.div_h), h = t - n * p.H;
               h0 = (int)h + p.pad; w0 = (int)w + p.pad; hlim = p.Ho; wlim = p.Wo;
-              base = p.dy + (((long long)n * p.Ho + (h0 >> sh)) * p.Wo + (w0 >> sh)) * p.Kc;
+              base = pdy + (((long long)n * p.Ho + (h0 >> sh)) * p.Wo + (w0 >> sh)) * p.Kc;
             }
             unsigned long long sbits = 0ull;
 #pragma unroll 1
@@ -287,8 +303,8 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
       int wb_r = 0, wb_s = 0, wb_c = 0;
       bool wb_ok = false;
       if (MODE == MODE_WGRAD) {
-        constexpr int CPR = BN / 8;
-        const uint32_t nn = n0 + (tid % CPR) * 8;
+        constexpr int CPR = BN / EPC;
+        const uint32_t nn = n0 + (tid % CPR) * EPC;
         wb_ok = nn < p.gemm_n;
         const uint32_t tap = fdiv(nn, p.div_c);
         wb_c = (int)(nn - tap * p.C);
@@ -307,7 +323,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
           // plain 2-D operand: fetched by TMA below
         } else if (MODE == MODE_FWD || MODE == MODE_DGRAD) {
           const uint32_t j = tid & 7;
-          const uint32_t k = kb * BK + j * 8;
+          const uint32_t k = kb * BK + j * EPC;
           const bool k_ok = k < p.gemm_k;
           const uint32_t cdim = (MODE == MODE_FWD) ? (uint32_t)p.C : (uint32_t)p.Kc;
           const uint32_t tap = fdiv(k, MODE == MODE_FWD ? p.div_c : p.div_kc);
@@ -326,19 +342,20 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
             const uint32_t row = (tid >> 3) + 16 * i;
             const bool ok = (rowmask[i] & bit) != 0ull;
             // the dummy source of a zero-filled chunk must be a mapped address: rowbase may point before the tensor
-            cp_async16(sa + swz(row, j), ok ? (rowbase[i] + off) : (MODE == MODE_FWD ? p.x : p.dy), ok);
+            cp_async16(sa + swz(row, j), ok ? (rowbase[i] + off) : (MODE == MODE_FWD ? px : pdy), ok);
           }
-        } else {  // WGRAD A^T: rows are positions, 16 chunks (128 co) per row
-          const uint32_t c = tid & 15;
-          const uint32_t co = m0 + c * 8;
+        } else {  // WGRAD A^T: rows are positions, BM/EPC chunks (128 co) per row
+          constexpr int CPRA = BM / EPC, RPPA = PRODUCERS / CPRA;
+          const uint32_t c = tid % CPRA;
+          const uint32_t co = m0 + c * EPC;
           const bool co_ok = co < p.gemm_m;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const uint32_t row = (tid >> 4) + 8 * i;
+          for (int i = 0; i < BK / RPPA; ++i) {
+            const uint32_t row = (tid / CPRA) + RPPA * i;
             const uint32_t pos = kb * BK + row;
             const bool ok = co_ok && pos < p.gemm_k;
-            const __nv_bfloat16* src = ok ? p.dy + ((size_t)pos * p.Kc + co) : p.dy;
-            cp_async16(sa + (c >> 3) * (BK * 128) + swz(row, c & 7), src, ok);
+            const T* src = ok ? pdy + ((size_t)pos * p.Kc + co) : pdy;
+            cp_async16(sa + (c >> 3) * (BK * 128) + swz_mn<T>(row, c & 7), src, ok);
           }
         }
 
@@ -347,34 +364,34 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
           // plain 2-D operand: fetched by TMA below
         } else if (MODE == MODE_FWD) {          // weight rows, K-major: BN rows x 8 chunks
           const uint32_t j = tid & 7;
-          const uint32_t k = kb * BK + j * 8;
+          const uint32_t k = kb * BK + j * EPC;
           const bool k_ok = k < p.gemm_k;
 #pragma unroll
           for (int i = 0; i < BN / 16; ++i) {
             const uint32_t row = (tid >> 3) + 16 * i;
             const uint32_t nn = n0 + row;
             const bool ok = k_ok && nn < p.gemm_n;
-            const __nv_bfloat16* src = ok ? p.w + ((size_t)nn * p.gemm_k + k) : p.w;
+            const T* src = ok ? pw + ((size_t)nn * p.gemm_k + k) : pw;
             cp_async16(sb + swz(row, j), src, ok);
           }
-        } else if (MODE == MODE_DGRAD) {  // B^T rows k=(r,s,co) -> weight row (co,r,s); BN/8 chunks of ci
-          constexpr int CPR = BN / 8;
+        } else if (MODE == MODE_DGRAD) {  // B^T rows k=(r,s,co) -> weight row (co,r,s); BN/EPC chunks of ci
+          constexpr int CPR = BN / EPC;
           constexpr int RPP = PRODUCERS / CPR;   // rows per pass
           const uint32_t c = tid % CPR;
-          const uint32_t ci = n0 + c * 8;
+          const uint32_t ci = n0 + c * EPC;
           const bool ci_ok = ci < p.gemm_n;
           if (p.cpt != 0 || (p.Kc % BK) == 0) {
-            // Cout multiple of 64: the 64 rows of this k-block share one tap and walk consecutive co
+            // Cout multiple of BK: the BK rows of this k-block share one tap and walk consecutive co
             const uint32_t k0 = kb * BK;
             const uint32_t tap = fdiv(k0, p.div_kc);
             const uint32_t co0 = k0 - tap * p.Kc;
             const size_t row_stride = (size_t)(p.R * p.S) * p.C;
-            const __nv_bfloat16* base = p.w + ((size_t)co0 * (p.R * p.S) + tap) * p.C + ci;
+            const T* base = pw + ((size_t)co0 * (p.R * p.S) + tap) * p.C + ci;
             const bool blk_ok = ci_ok && k0 < p.gemm_k;
 #pragma unroll
             for (int i = 0; i < BK / RPP; ++i) {
               const uint32_t row = (tid / CPR) + RPP * i;
-              cp_async16(sb + (c >> 3) * (BK * 128) + swz(row, c & 7), blk_ok ? base + row * row_stride : p.w, blk_ok);
+              cp_async16(sb + (c >> 3) * (BK * 128) + swz_mn<T>(row, c & 7), blk_ok ? base + row * row_stride : pw, blk_ok);
             }
           } else {
 #pragma unroll 1
@@ -384,12 +401,12 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
               const bool ok = ci_ok && k < p.gemm_k;
               const uint32_t tap = fdiv(k, p.div_kc);
               const uint32_t co = k - tap * p.Kc;
-              const __nv_bfloat16* src = ok ? p.w + (((size_t)co * (p.R * p.S) + tap) * p.C + ci) : p.w;
-              cp_async16(sb + (c >> 3) * (BK * 128) + swz(row, c & 7), src, ok);
+              const T* src = ok ? pw + (((size_t)co * (p.R * p.S) + tap) * p.C + ci) : pw;
+              cp_async16(sb + (c >> 3) * (BK * 128) + swz_mn<T>(row, c & 7), src, ok);
             }
           }
         } else {  // WGRAD B^T: rows are positions, chunk column fixed (r,s,ci)
-          constexpr int CPR = BN / 8;
+          constexpr int CPR = BN / EPC;
           constexpr int RPP = PRODUCERS / CPR;
           const uint32_t c = tid % CPR;
 #pragma unroll
@@ -397,15 +414,15 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
             const uint32_t row = (tid / CPR) + RPP * i;
             const uint32_t pos = kb * BK + row;
             bool ok = wb_ok && pos < p.gemm_k;
-            const __nv_bfloat16* src = p.x;
+            const T* src = px;
             if (ok) {
               const uint32_t t = fdiv(pos, p.div_wo), wo = pos - t * p.Wo;
               const uint32_t n = fdiv(t, p.div_ho), ho = t - n * p.Ho;
               const int h = (int)ho * p.stride - p.pad + wb_r, w = (int)wo * p.stride - p.pad + wb_s;
               ok = h >= 0 && h < p.H && w >= 0 && w < p.W;
-              if (ok) src = p.x + ((((size_t)n * p.H + h) * p.W + w) * p.C + wb_c);
+              if (ok) src = px + ((((size_t)n * p.H + h) * p.W + w) * p.C + wb_c);
             }
-            cp_async16(sb + (c >> 3) * (BK * 128) + swz(row, c & 7), src, ok);
+            cp_async16(sb + (c >> 3) * (BK * 128) + swz_mn<T>(row, c & 7), src, ok);
           }
         }
         if ((p.a_tma | p.b_tma) && tid == 0) {
@@ -414,9 +431,10 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
           const uint32_t bytes = (p.a_tma ? (uint32_t)C::A_BYTES : 0u) + (p.b_tma ? (uint32_t)C::B_BYTES : 0u);
           mbar_arrive_expect_tx(&full_bar[stage], bytes);
           if (p.a_tma) {
-            if (MODE == MODE_WGRAD) {         // A^T tile: 64 positions x 128 co as two 64-wide groups
-              tma_load_2d(sa, &tmA, (int)m0, (int)(kb * BK), &full_bar[stage]);
-              tma_load_2d(sa + BK * 128, &tmA, (int)m0 + 64, (int)(kb * BK), &full_bar[stage]);
+            if (MODE == MODE_WGRAD) {         // A^T tile: BK positions x 128 co as 128-byte-wide groups (2 bf16 / 4 fp32)
+#pragma unroll
+              for (int gidx = 0; gidx < BM / BK; ++gidx)
+                tma_load_2d(sa + gidx * (BK * 128), &tmA, (int)m0 + gidx * BK, (int)(kb * BK), &full_bar[stage]);
             } else {                          // [M][K] matrix (1x1 conv, stride 1 / linear)
               tma_load_2d(sa, &tmA, (int)(kb * BK), (int)m0, &full_bar[stage]);
             }
@@ -463,7 +481,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
             for (int q = 0; q < 32; ++q) f[q] = 0.f;
           }
           if (MODE == MODE_FWD && p.bn_sums != nullptr) bn_stats_accumulate<32>(p, n0 + cb * 32, f, lane);
-          epilogue_store<MODE, 32>(p, m, n0 + cb * 32, f);
+          epilogue_store<T, MODE, 32>(p, m, n0 + cb * 32, f);
         }
       }
     } else {
@@ -485,7 +503,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
     }
   } else if (lane == 0 && nkb > 0) {
     // =============================== MMA ISSUER (one thread) ===============================
-    constexpr uint32_t idesc = make_idesc(BM, BN, C::A_MN ? 1 : 0, C::B_MN ? 1 : 0);
+    constexpr uint32_t idesc = make_idesc(BM, BN, C::A_MN ? 1 : 0, C::B_MN ? 1 : 0, El<T>::FMT);
     const uint32_t smem_base = smem_u32(smem);
     for (uint32_t it = 0; it < nkb; ++it) {
       const uint32_t stage = it % STAGES, ph = (it / STAGES) & 1;
@@ -493,11 +511,12 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
       tc_fence_after();
       const uint32_t sa = smem_base + stage * C::STAGE_BYTES, sb = sa + C::A_BYTES;
 #pragma unroll
-      for (int k = 0; k < BK / 16; ++k) {
-        // K-major: +32 B per K=16 inside the 128-B swizzle row.  MN-major: +2 row groups (2048 B).
-        const uint64_t da = C::A_MN ? make_desc(sa + k * 2048, BK * 128, 1024) : make_desc(sa + k * 32, 16, 1024);
-        const uint64_t db = C::B_MN ? make_desc(sb + k * 2048, BK * 128, 1024) : make_desc(sb + k * 32, 16, 1024);
-        umma_bf16(tmem_base, da, db, idesc, (it | (uint32_t)k) != 0 ? 1u : 0u);
+      for (int k = 0; k < BK / El<T>::UK; ++k) {
+        // K-major: +32 B per MMA (16 bf16 / 8 fp32) inside the 128-B swizzle row.  MN-major: the UK k-rows of one MMA are
+        // 2048 B (bf16: two 8-row atoms) or 1024 B (fp32: two 4-row atoms) further on; 128-byte MN groups are BK*128 B apart.
+        const uint64_t da = C::A_MN ? make_desc_mn<T>(sa + k * (El<T>::UK * 128), BK * 128) : make_desc(sa + k * 32, 16, 1024);
+        const uint64_t db = C::B_MN ? make_desc_mn<T>(sb + k * (El<T>::UK * 128), BK * 128) : make_desc(sb + k * 32, 16, 1024);
+        umma<T>(tmem_base, da, db, idesc, (it | (uint32_t)k) != 0 ? 1u : 0u);
       }
       umma_commit(&empty_bar[stage]);            // ring slot free once these MMAs retire
       if (it + 1 == nkb) umma_commit(tmem_full);  // accumulator complete
@@ -525,7 +544,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
         for (int q = 0; q < SLICE; ++q) f[q] += ld_dsmem_f32(base + (uint32_t)q * BM * 4u);
       }
       if (MODE == MODE_FWD && p.bn_sums != nullptr) bn_stats_accumulate<SLICE>(p, n0 + rank * SLICE, f, lane);
-      if (MODE != MODE_WGRAD || p.nvk > 0) epilogue_store<MODE, SLICE>(p, m, n0 + rank * SLICE, f);
+      if (MODE != MODE_WGRAD || p.nvk > 0) epilogue_store<T, MODE, SLICE>(p, m, n0 + rank * SLICE, f);
     }
     STAMP(6, 0);
     cluster_sync_relaxed();  // nobody leaves while a peer may still read its shared memory (no memory ordering needed)
@@ -544,12 +563,12 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
 // tiles per SM from which the 3-stage / 2-CTAs-per-SM variant is used (B200DDP_TWO_CTA_TILES; 0 = never)
 static const uint32_t g_two_cta_tiles = []() { const char* e = getenv("B200DDP_TWO_CTA_TILES"); const int v = e ? atoi(e) : 2; return (uint32_t)(v < 1 ? 1000000 : v); }();
 
-template <int MODE, int BN, int ZC, int ST = 6>
+template <typename T, int MODE, int BN, int ZC, int ST = 6>
 int launch_zc(const ConvParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, dim3 grid, cudaStream_t s) {
-  using C = Cfg<MODE, BN, ST>;
+  using C = Cfg<T, MODE, BN, ST>;
   static bool attr_set = false;
   if (!attr_set) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<MODE, BN, ZC, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel<T, MODE, BN, ZC, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
     attr_set = true;
   }
   cudaLaunchConfig_t cfg;
@@ -574,20 +593,20 @@ int launch_zc(const ConvParams& p, const CUtensorMap& tmA, const CUtensorMap& tm
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<MODE, BN, ZC, ST>, p, tmA, tmB));
+  B200_CHECK_CUDA(cudaLaunchKernelEx(&cfg, conv_tc_kernel<T, MODE, BN, ZC, ST>, p, tmA, tmB));
   return 0;
 }
 
-template <int MODE, int BN>
+template <typename T, int MODE, int BN>
 int launch(const ConvParams& p, const CUtensorMap& tmA, const CUtensorMap& tmB, dim3 grid, uint32_t zc, cudaStream_t s) {
   switch (zc) {
     case 1:
       // many tiles per SM: two smaller CTAs per SM overlap each other's load latency and epilogue
-      if ((size_t)grid.x * grid.y >= (size_t)g_two_cta_tiles * b200_num_sms()) return launch_zc<MODE, BN, 1, 3>(p, tmA, tmB, grid, s);
-      return launch_zc<MODE, BN, 1>(p, tmA, tmB, grid, s);
-    case 2: return launch_zc<MODE, BN, 2>(p, tmA, tmB, grid, s);
-    case 4: return launch_zc<MODE, BN, 4>(p, tmA, tmB, grid, s);
-    case 8: return launch_zc<MODE, BN, 8>(p, tmA, tmB, grid, s);
+      if ((size_t)grid.x * grid.y >= (size_t)g_two_cta_tiles * b200_num_sms()) return launch_zc<T, MODE, BN, 1, 3>(p, tmA, tmB, grid, s);
+      return launch_zc<T, MODE, BN, 1>(p, tmA, tmB, grid, s);
+    case 2: return launch_zc<T, MODE, BN, 2>(p, tmA, tmB, grid, s);
+    case 4: return launch_zc<T, MODE, BN, 4>(p, tmA, tmB, grid, s);
+    case 8: return launch_zc<T, MODE, BN, 8>(p, tmA, tmB, grid, s);
     default: b200_set_error("cluster split %u is not 1, 2, 4 or 8", zc); return B200_ERR_ARG;
   }
 }
@@ -614,16 +633,20 @@ EncodeTiledFn encode_tiled_fn() {
   }
   return g_use_tma ? fn : nullptr;
 }
-// bf16 row-major matrix [outer][inner] -> boxes of box_outer rows x 64 elements (128 B), 128B swizzle
-bool make_tmap_2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint32_t box_outer) {
+// row-major matrix [outer][inner] of T -> boxes of box_outer rows x 128 bytes (64 bf16 / 32 fp32), 128B swizzle.
+// mn_major: the box is an MN-major operand tile (rows are k): 32-bit elements then need the 32-byte-atom swizzle.
+template <typename T>
+bool make_tmap_2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t outer, uint32_t box_outer, bool mn_major = false) {
   EncodeTiledFn fn = encode_tiled_fn();
-  if (fn == nullptr || (reinterpret_cast<uintptr_t>(base) & 15) != 0 || (inner * 2) % 16 != 0) return false;
+  constexpr uint64_t ES = sizeof(T);
+  if (fn == nullptr || (reinterpret_cast<uintptr_t>(base) & 15) != 0 || (inner * ES) % 16 != 0) return false;
   cuuint64_t dims[2] = {inner, outer};
-  cuuint64_t strides[1] = {inner * 2};
-  cuuint32_t box[2] = {64, box_outer};
+  cuuint64_t strides[1] = {inner * ES};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / ES), box_outer};
   cuuint32_t estr[2] = {1, 1};
-  return fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+  const CUtensorMapSwizzle sw = (mn_major && ES == 4) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+  return fn(m, ES == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims,
+            strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
@@ -667,8 +690,8 @@ int fill_common(ConvParams& p, const b200_conv_geom* g) {
   return 0;
 }
 
-// K-loop plan for FWD/DGRAD: `cdim` = channels per tap along K
-void plan_k(ConvParams& p, uint32_t cdim) {
+// K-loop plan for FWD/DGRAD: `cdim` = channels per tap along K, BK = K elements per k-block
+void plan_k(ConvParams& p, uint32_t cdim, uint32_t BK) {
   const uint32_t kblocks = (p.gemm_k + BK - 1) / BK;
   int ntaps_valid = 0;
   for (int t = 0; t < 64; ++t) ntaps_valid += (int)((p.tapmask >> t) & 1ull);
@@ -726,6 +749,7 @@ extern "C" int b200_conv_set_split_k(int enabled) {
   return 0;
 }
 
+template <typename T>
 static int conv_fwd_impl(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g, int relu,
                          float* bn_sums, void* stream) {
   ConvParams p;
@@ -733,9 +757,9 @@ static int conv_fwd_impl(const void* x, const void* w, const float* bias, void* 
   if (rc) return rc;
   B200_REQUIRE(x && w && y, "null tensor");
   B200_REQUIRE(bn_sums == nullptr || (bias == nullptr && !relu), "BN statistics are taken of the raw conv output: no bias, no ReLU");
-  p.x = (const __nv_bfloat16*)x; p.w = (const __nv_bfloat16*)w; p.out = y; p.bias = bias; p.relu = relu; p.bn_sums = bn_sums;
+  p.x = x; p.w = w; p.out = y; p.bias = bias; p.relu = relu; p.bn_sums = bn_sums;
   p.gemm_m = (uint32_t)p.N * p.Ho * p.Wo; p.gemm_n = p.Kc; p.gemm_k = (uint32_t)p.R * p.S * p.C;
-  plan_k(p, p.C);
+  plan_k(p, p.C, El<T>::BK);
   const bool narrow = p.gemm_n <= 64;
   const uint32_t bn = narrow ? 64 : 128;
   dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, 1);
@@ -744,16 +768,20 @@ static int conv_fwd_impl(const void* x, const void* w, const float* bias, void* 
   CUtensorMap tmA, tmB;
   memset(&tmA, 0, sizeof(tmA));
   memset(&tmB, 0, sizeof(tmB));
-  p.b_tma = make_tmap_2d(&tmB, w, p.gemm_k, p.gemm_n, bn) ? 1u : 0u;                       // weights [Cout][R*S*C]
+  p.b_tma = make_tmap_2d<T>(&tmB, w, p.gemm_k, p.gemm_n, bn) ? 1u : 0u;                       // weights [Cout][R*S*C]
   const bool plain = p.R == 1 && p.S == 1 && p.stride == 1 && p.pad == 0;
-  p.a_tma = (plain && make_tmap_2d(&tmA, x, p.gemm_k, p.gemm_m, BM)) ? 1u : 0u;             // x as [M][C]
-  return narrow ? launch<MODE_FWD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
-                : launch<MODE_FWD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
+  p.a_tma = (plain && make_tmap_2d<T>(&tmA, x, p.gemm_k, p.gemm_m, BM)) ? 1u : 0u;             // x as [M][C]
+  return narrow ? launch<T, MODE_FWD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
+                : launch<T, MODE_FWD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
 }
 
 extern "C" int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g,
                              int relu, void* stream) {
-  return conv_fwd_impl(x, w, bias, y, g, relu, nullptr, stream);
+  return conv_fwd_impl<__nv_bfloat16>(x, w, bias, y, g, relu, nullptr, stream);
+}
+extern "C" int b200_conv_fwd_f32(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g,
+                                 int relu, void* stream) {
+  return conv_fwd_impl<float>(x, w, bias, y, g, relu, nullptr, stream);
 }
 
 // Same convolution (no bias, no ReLU), and the epilogue also adds the per-channel sum and sum of squares of the fp32
@@ -762,9 +790,15 @@ extern "C" int b200_conv_fwd(const void* x, const void* w, const float* bias, vo
 extern "C" int b200_conv_fwd_stats(const void* x, const void* w, void* y, const b200_conv_geom* g, float* bn_sums,
                                    void* stream) {
   B200_REQUIRE(bn_sums != nullptr, "null bn_sums");
-  return conv_fwd_impl(x, w, nullptr, y, g, 0, bn_sums, stream);
+  return conv_fwd_impl<__nv_bfloat16>(x, w, nullptr, y, g, 0, bn_sums, stream);
+}
+extern "C" int b200_conv_fwd_stats_f32(const void* x, const void* w, void* y, const b200_conv_geom* g, float* bn_sums,
+                                       void* stream) {
+  B200_REQUIRE(bn_sums != nullptr, "null bn_sums");
+  return conv_fwd_impl<float>(x, w, nullptr, y, g, 0, bn_sums, stream);
 }
 
+template <typename T>
 static int conv_dgrad_impl(const void* dy, const void* w, void* dx, const b200_conv_geom* g, const void* residual,
                            void* stream) {
   ConvParams p;
@@ -772,9 +806,9 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, const b200_c
   if (rc) return rc;
   B200_REQUIRE(dy && w && dx, "null tensor");
   B200_REQUIRE(p.stride <= 2, "dgrad supports stride 1 and 2");
-  p.dy = (const __nv_bfloat16*)dy; p.w = (const __nv_bfloat16*)w; p.out = dx; p.residual = (const __nv_bfloat16*)residual;
+  p.dy = dy; p.w = w; p.out = dx; p.residual = residual;
   p.gemm_m = (uint32_t)p.N * p.H * p.W; p.gemm_n = p.C; p.gemm_k = (uint32_t)p.R * p.S * p.Kc;
-  plan_k(p, p.Kc);
+  plan_k(p, p.Kc, El<T>::BK);
   const bool narrow = p.gemm_n <= 64;
   const uint32_t bn = narrow ? 64 : 128;
   dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, 1);
@@ -784,30 +818,39 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, const b200_c
   memset(&tmA, 0, sizeof(tmA));
   memset(&tmB, 0, sizeof(tmB));
   const bool plain = p.R == 1 && p.S == 1 && p.stride == 1 && p.pad == 0;
-  p.a_tma = (plain && make_tmap_2d(&tmA, dy, p.gemm_k, p.gemm_m, BM)) ? 1u : 0u;            // dy as [M][Cout]
-  return narrow ? launch<MODE_DGRAD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
-                : launch<MODE_DGRAD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
+  p.a_tma = (plain && make_tmap_2d<T>(&tmA, dy, p.gemm_k, p.gemm_m, BM)) ? 1u : 0u;            // dy as [M][Cout]
+  return narrow ? launch<T, MODE_DGRAD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
+                : launch<T, MODE_DGRAD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
 }
 
 extern "C" int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream) {
-  return conv_dgrad_impl(dy, w, dx, g, nullptr, stream);
+  return conv_dgrad_impl<__nv_bfloat16>(dy, w, dx, g, nullptr, stream);
+}
+extern "C" int b200_conv_dgrad_f32(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream) {
+  return conv_dgrad_impl<float>(dy, w, dx, g, nullptr, stream);
 }
 
-// dx = dgrad(dy, w) + residual (bf16, same shape as dx): when the conv's input also feeds another branch (a ResNet skip
+// dx = dgrad(dy, w) + residual (same dtype and shape as dx): when the conv's input also feeds another branch (a ResNet skip
 // connection), that branch's gradient is added in the epilogue instead of by a separate elementwise kernel.
 extern "C" int b200_conv_dgrad_add(const void* dy, const void* w, void* dx, const b200_conv_geom* g, const void* residual,
                                    void* stream) {
   B200_REQUIRE(residual != nullptr, "null residual");
-  return conv_dgrad_impl(dy, w, dx, g, residual, stream);
+  return conv_dgrad_impl<__nv_bfloat16>(dy, w, dx, g, residual, stream);
+}
+extern "C" int b200_conv_dgrad_add_f32(const void* dy, const void* w, void* dx, const b200_conv_geom* g, const void* residual,
+                                       void* stream) {
+  B200_REQUIRE(residual != nullptr, "null residual");
+  return conv_dgrad_impl<float>(dy, w, dx, g, residual, stream);
 }
 
-extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
-                               void* stream) {
+template <typename T>
+static int conv_wgrad_impl(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits, void* stream) {
+  constexpr uint32_t BK = El<T>::BK;
   ConvParams p;
   int rc = fill_common(p, g);
   if (rc) return rc;
   B200_REQUIRE(x && dy && dw, "null tensor");
-  p.x = (const __nv_bfloat16*)x; p.dy = (const __nv_bfloat16*)dy; p.out = dw;
+  p.x = x; p.dy = dy; p.out = dw;
   p.gemm_m = p.Kc; p.gemm_n = (uint32_t)p.R * p.S * p.C; p.gemm_k = (uint32_t)p.N * p.Ho * p.Wo;
   const uint32_t kblocks = (p.gemm_k + BK - 1) / BK;
   p.nvk = kblocks;
@@ -851,7 +894,16 @@ extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b
   CUtensorMap tmA, tmB;
   memset(&tmA, 0, sizeof(tmA));
   memset(&tmB, 0, sizeof(tmB));
-  p.a_tma = make_tmap_2d(&tmA, dy, p.gemm_m, p.gemm_k, BK) ? 1u : 0u;      // dy as [positions][Cout], 64 x 64 boxes
-  return narrow ? launch<MODE_WGRAD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
-                : launch<MODE_WGRAD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
+  p.a_tma = make_tmap_2d<T>(&tmA, dy, p.gemm_m, p.gemm_k, BK, /*mn_major=*/true) ? 1u : 0u;   // dy as [positions][Cout], BK x 128-byte boxes
+  return narrow ? launch<T, MODE_WGRAD, 64>(p, tmA, tmB, grid, zc, (cudaStream_t)stream)
+                : launch<T, MODE_WGRAD, 128>(p, tmA, tmB, grid, zc, (cudaStream_t)stream);
+}
+
+extern "C" int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
+                               void* stream) {
+  return conv_wgrad_impl<__nv_bfloat16>(x, dy, dw, g, max_splits, stream);
+}
+extern "C" int b200_conv_wgrad_f32(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
+                                   void* stream) {
+  return conv_wgrad_impl<float>(x, dy, dw, g, max_splits, stream);
 }

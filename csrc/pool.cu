@@ -7,12 +7,14 @@
 //  trojan_stamp       batched alpha-blend of a trigger pattern (model_lib/cifar10_cnn_model.py:77-84,
 //                     mnist_cnn_model.py:74-81, audio_rnn_model.py:77-83).
 #include "common.cuh"
+#include "act8.cuh"
 
 namespace {
 
 // one thread per (n, ho, wo, 8-channel vector)
+template <typename T>
 __global__ void __launch_bounds__(256)
-maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, uint8_t* __restrict__ amax,
+maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ amax,
                    int N, int H, int W, int C, int Ho, int Wo, int k, int stride, int pad) {
   pdl_trigger();
   pdl_wait();
@@ -36,13 +38,13 @@ maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
         const int w = wo * stride - pad + s;
         if (w < 0 || w >= W) continue;
         float f[8];
-        bf16x8_to_float(*reinterpret_cast<const bf16x8*>(x + (((size_t)n * H + h) * W + w) * C + cv * 8), f);
+        act8_to_float(ld_act8(x + (((size_t)n * H + h) * W + w) * C + cv * 8), f);
 #pragma unroll
         for (int q = 0; q < 8; ++q)
           if (f[q] > best[q]) { best[q] = f[q]; bi[q] = (uint8_t)(r * k + s); }
       }
     }
-    *reinterpret_cast<bf16x8*>(y + i * 8) = float_to_bf16x8(best);
+    st_act8(y + i * 8, best);
     if (amax) {
       uint2 packed;
       packed.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
@@ -53,9 +55,10 @@ maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
 }
 
 // gather form: one thread per input (n,h,w,8ch); visits the <= ceil(k/stride)^2 windows that cover it
+template <typename T>
 __global__ void __launch_bounds__(256)
-maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restrict__ amax,
-                   __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int k, int stride,
+maxpool_bwd_kernel(const T* __restrict__ dy, const uint8_t* __restrict__ amax,
+                   T* __restrict__ dx, int N, int H, int W, int C, int Ho, int Wo, int k, int stride,
                    int pad) {
   pdl_trigger();
   pdl_wait();
@@ -82,7 +85,7 @@ maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restri
         const size_t o = ((((size_t)n * Ho + ho) * Wo + wo) * CV + cv) * 8;
         const uint2 packed = *reinterpret_cast<const uint2*>(amax + o);
         float g[8];
-        bf16x8_to_float(*reinterpret_cast<const bf16x8*>(dy + o), g);
+        act8_to_float(ld_act8(dy + o), g);
         const uint8_t me = (uint8_t)(r * k + s);
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
@@ -91,13 +94,14 @@ maxpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const uint8_t* __restri
         }
       }
     }
-    *reinterpret_cast<bf16x8*>(dx + i * 8) = float_to_bf16x8(acc);
+    st_act8(dx + i * 8, acc);
   }
 }
 
 // x [N][HW][C] -> y [N][C] (mean over HW); one thread per (n, 8ch)
+template <typename T>
 __global__ void __launch_bounds__(256)
-avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int HW, int C) {
+avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int N, int HW, int C) {
   pdl_trigger();
   pdl_wait();
   const int CV = C / 8;
@@ -109,18 +113,19 @@ avgpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restric
   for (int q = 0; q < 8; ++q) acc[q] = 0.f;
   for (int p = 0; p < HW; ++p) {
     float f[8];
-    bf16x8_to_float(*reinterpret_cast<const bf16x8*>(x + ((size_t)n * HW + p) * C + cv * 8), f);
+    act8_to_float(ld_act8(x + ((size_t)n * HW + p) * C + cv * 8), f);
 #pragma unroll
     for (int q = 0; q < 8; ++q) acc[q] += f[q];
   }
   const float inv = 1.f / (float)HW;
 #pragma unroll
   for (int q = 0; q < 8; ++q) acc[q] *= inv;
-  *reinterpret_cast<bf16x8*>(y + (size_t)n * C + cv * 8) = float_to_bf16x8(acc);
+  st_act8(y + (size_t)n * C + cv * 8, acc);
 }
 
+template <typename T>
 __global__ void __launch_bounds__(256)
-avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int HW, int C) {
+avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int N, int HW, int C) {
   pdl_trigger();
   pdl_wait();
   const int CV = C / 8;
@@ -130,28 +135,30 @@ avgpool_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restri
     const int cv = (int)(i % CV);
     const int n = (int)(i / ((size_t)HW * CV));
     float f[8];
-    bf16x8_to_float(*reinterpret_cast<const bf16x8*>(dy + (size_t)n * C + cv * 8), f);
+    act8_to_float(ld_act8(dy + (size_t)n * C + cv * 8), f);
 #pragma unroll
     for (int q = 0; q < 8; ++q) f[q] *= inv;
-    *reinterpret_cast<bf16x8*>(dx + i * 8) = float_to_bf16x8(f);
+    st_act8(dx + i * 8, f);
   }
 }
 
+template <typename T>
 __global__ void __launch_bounds__(256)
-relu_bwd_kernel(const bf16x8* __restrict__ dy, const bf16x8* __restrict__ y, bf16x8* __restrict__ dx, size_t n8) {
+relu_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ y, T* __restrict__ dx, size_t n8) {
   pdl_trigger();
   pdl_wait();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
     float g[8], v[8];
-    bf16x8_to_float(dy[i], g);
-    bf16x8_to_float(y[i], v);
+    act8_to_float(ld_act8(dy + i * 8), g);
+    act8_to_float(ld_act8(y + i * 8), v);
 #pragma unroll
     for (int q = 0; q < 8; ++q) g[q] = v[q] > 0.f ? g[q] : 0.f;
-    dx[i] = float_to_bf16x8(g);
+    st_act8(dx + i * 8, g);
   }
 }
 
-// layout 0: out NHWC bf16 with C_out >= C channels (extra channels zero) ; layout 1: out NCHW fp32 (C_out == C)
+// layout 0: out NHWC bf16 with C_out >= C channels (extra channels zero) ; layout 1: out NCHW fp32 (C_out == C) ;
+// layout 2: out NHWC fp32 with C_out >= C channels (the fp32 activation path)
 __global__ void __launch_bounds__(256)
 augment_kernel(const uint8_t* __restrict__ img, const int32_t* __restrict__ offsets, void* __restrict__ out, int N,
                int H, int W, int C, int C_out, int pad, const float* __restrict__ mean,
@@ -173,7 +180,14 @@ augment_kernel(const uint8_t* __restrict__ img, const int32_t* __restrict__ offs
     const int sh = h + dy - pad, sw = wc + dx - pad;  // source pixel in the unpadded image
     const bool inside = sh >= 0 && sh < H && sw >= 0 && sw < W;
     const uint8_t* src = img + (((size_t)n * H + sh) * W + sw) * C;
-    if (layout == 0) {
+    if (layout == 2) {
+      float* o = reinterpret_cast<float*>(out) + i * C_out;
+      for (int c = 0; c < C_out; ++c) {
+        float v = 0.f;
+        if (c < C) v = ((inside ? (float)src[c] * (1.f / 255.f) : 0.f) - mean[c]) * inv_std[c];
+        o[c] = v;
+      }
+    } else if (layout == 0) {
       __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(out) + i * C_out;
       for (int c = 0; c < C_out; ++c) {
         float v = 0.f;
@@ -210,8 +224,9 @@ trojan_stamp_kernel(float* __restrict__ x, int N, int C, int H, int W, const flo
 
 
 // dbias[c] += sum_rows dy[row][c]   (bias gradient of conv / linear layers; fp32 atomics into the arena)
+template <typename T>
 __global__ void __launch_bounds__(256)
-colsum_accum_kernel(const __nv_bfloat16* __restrict__ dy, size_t rows, int C, int c_valid, float* __restrict__ out) {
+colsum_accum_kernel(const T* __restrict__ dy, size_t rows, int C, int c_valid, float* __restrict__ out) {
   pdl_trigger();
   pdl_wait();
   __shared__ float sm[32][64];
@@ -223,7 +238,7 @@ colsum_accum_kernel(const __nv_bfloat16* __restrict__ dy, size_t rows, int C, in
   if (c < C) {
     for (size_t r = (size_t)blockIdx.x * 32 + rl; r < rows; r += (size_t)gridDim.x * 32) {
       float f[8];
-      bf16x8_to_float(*reinterpret_cast<const bf16x8*>(dy + r * C + c), f);
+      act8_to_float(ld_act8(dy + r * C + c), f);
 #pragma unroll
       for (int k = 0; k < 8; ++k) acc[k] += f[k];
     }
@@ -242,58 +257,79 @@ colsum_accum_kernel(const __nv_bfloat16* __restrict__ dy, size_t rows, int C, in
 
 }  // namespace
 
-extern "C" int b200_maxpool_fwd(const void* x, void* y, uint8_t* argmax, int N, int H, int W, int C, int k, int stride,
-                                int pad, void* stream) {
+// Every activation-touching entry point exists for both activation dtypes: `name` (NHWC bf16) and `name_f32` (NHWC fp32).
+#define B200_POOL_BOTH(name, params, args)                                                \
+  extern "C" int name params { return name##_impl<__nv_bfloat16> args; }                  \
+  extern "C" int name##_f32 params { return name##_impl<float> args; }
+
+template <typename T>
+static int b200_maxpool_fwd_impl(const void* x, void* y, uint8_t* argmax, int N, int H, int W, int C, int k, int stride, int pad,
+                                 void* stream) {
   B200_REQUIRE(x && y, "null argument");
   B200_REQUIRE(C % 8 == 0 && k * k <= 255 && stride > 0, "C must be a multiple of 8");
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const size_t total = (size_t)N * Ho * Wo * (C / 8);
-  b200_launch(maxpool_fwd_kernel, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 
-      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, argmax, N, H, W, C, Ho, Wo, k, stride, pad);
+  b200_launch(maxpool_fwd_kernel<T>, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, (const T*)x, (T*)y,
+              argmax, N, H, W, C, Ho, Wo, k, stride, pad);
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_POOL_BOTH(b200_maxpool_fwd,
+               (const void* x, void* y, uint8_t* argmax, int N, int H, int W, int C, int k, int stride, int pad, void* stream),
+               (x, y, argmax, N, H, W, C, k, stride, pad, stream))
 
-extern "C" int b200_maxpool_bwd(const void* dy, const uint8_t* argmax, void* dx, int N, int H, int W, int C, int k,
-                                int stride, int pad, void* stream) {
+template <typename T>
+static int b200_maxpool_bwd_impl(const void* dy, const uint8_t* argmax, void* dx, int N, int H, int W, int C, int k, int stride,
+                                 int pad, void* stream) {
   B200_REQUIRE(dy && argmax && dx, "null argument");
   B200_REQUIRE(C % 8 == 0, "C must be a multiple of 8");
   const int Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
   const size_t total = (size_t)N * H * W * (C / 8);
-  b200_launch(maxpool_bwd_kernel, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, 
-      (const __nv_bfloat16*)dy, argmax, (__nv_bfloat16*)dx, N, H, W, C, Ho, Wo, k, stride, pad);
+  b200_launch(maxpool_bwd_kernel<T>, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, (const T*)dy, argmax,
+              (T*)dx, N, H, W, C, Ho, Wo, k, stride, pad);
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_POOL_BOTH(b200_maxpool_bwd,
+               (const void* dy, const uint8_t* argmax, void* dx, int N, int H, int W, int C, int k, int stride, int pad, void* stream),
+               (dy, argmax, dx, N, H, W, C, k, stride, pad, stream))
 
-extern "C" int b200_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream) {
+template <typename T>
+static int b200_avgpool_fwd_impl(const void* x, void* y, int N, int HW, int C, void* stream) {
   B200_REQUIRE(x && y && C % 8 == 0, "bad argument");
   const int total = N * (C / 8);
-  b200_launch(avgpool_fwd_kernel, dim3((total + 255) / 256), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, HW, C);
+  b200_launch(avgpool_fwd_kernel<T>, dim3((total + 255) / 256), dim3(256), 0, (cudaStream_t)stream, (const T*)x, (T*)y, N, HW, C);
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_POOL_BOTH(b200_avgpool_fwd, (const void* x, void* y, int N, int HW, int C, void* stream), (x, y, N, HW, C, stream))
 
-extern "C" int b200_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream) {
+template <typename T>
+static int b200_avgpool_bwd_impl(const void* dy, void* dx, int N, int HW, int C, void* stream) {
   B200_REQUIRE(dy && dx && C % 8 == 0, "bad argument");
   const size_t total = (size_t)N * HW * (C / 8);
-  b200_launch(avgpool_bwd_kernel, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, HW, C);
+  b200_launch(avgpool_bwd_kernel<T>, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, (const T*)dy, (T*)dx, N,
+              HW, C);
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_POOL_BOTH(b200_avgpool_bwd, (const void* dy, void* dx, int N, int HW, int C, void* stream), (dy, dx, N, HW, C, stream))
 
-extern "C" int b200_relu_bwd(const void* dy, const void* y, void* dx, size_t n, void* stream) {
+template <typename T>
+static int b200_relu_bwd_impl(const void* dy, const void* y, void* dx, size_t n, void* stream) {
   B200_REQUIRE(dy && y && dx && n % 8 == 0, "n must be a multiple of 8");
   if (n == 0) return 0;
-  b200_launch(relu_bwd_kernel, dim3(b200_grid_for(n / 8, 256, 8)), dim3(256), 0, (cudaStream_t)stream, (const bf16x8*)dy, (const bf16x8*)y, (bf16x8*)dx, n / 8);
+  b200_launch(relu_bwd_kernel<T>, dim3(b200_grid_for(n / 8, 256, 8)), dim3(256), 0, (cudaStream_t)stream, (const T*)dy, (const T*)y,
+              (T*)dx, n / 8);
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_POOL_BOTH(b200_relu_bwd, (const void* dy, const void* y, void* dx, size_t n, void* stream), (dy, y, dx, n, stream))
 
 extern "C" int b200_augment(const uint8_t* img_u8, const int32_t* offsets, void* out, int N, int H, int W, int C,
                             int C_out, int pad, const float* mean, const float* inv_std, int layout, void* stream) {
   B200_REQUIRE(img_u8 && out && mean && inv_std, "null argument");
-  B200_REQUIRE(layout == 0 || (layout == 1 && C_out == C), "layout 1 (NCHW fp32) needs C_out == C");
+  B200_REQUIRE(layout == 0 || layout == 2 || (layout == 1 && C_out == C), "layout 1 (NCHW fp32) needs C_out == C");
   B200_REQUIRE(C_out >= C, "C_out < C");
   const size_t total = (size_t)N * H * W;
   b200_launch(augment_kernel, dim3(b200_grid_for(total, 256, 8)), dim3(256), 0, (cudaStream_t)stream, img_u8, offsets, out, N, H, W, C, C_out, pad, mean, inv_std, layout);
@@ -313,14 +349,17 @@ extern "C" int b200_trojan_stamp(float* x, int N, int C, int H, int W, const flo
   return 0;
 }
 
-extern "C" int b200_colsum_accum(const void* dy_bf16, size_t rows, int C, int c_valid, float* out, void* stream) {
-  B200_REQUIRE(dy_bf16 && out && C % 8 == 0 && c_valid <= C, "bad argument");
+template <typename T>
+static int b200_colsum_accum_impl(const void* dy, size_t rows, int C, int c_valid, float* out, void* stream) {
+  B200_REQUIRE(dy && out && C % 8 == 0 && c_valid <= C, "bad argument");
   if (rows == 0) return 0;
   size_t rb = rows / 64;
   if (rb < 1) rb = 1;
   if (rb > 64) rb = 64;
   dim3 grid((unsigned)rb, (unsigned)((C + 63) / 64), 1);
-  b200_launch(colsum_accum_kernel, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const __nv_bfloat16*)dy_bf16, rows, C, c_valid, out);
+  b200_launch(colsum_accum_kernel<T>, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const T*)dy, rows, C, c_valid, out);
   B200_CHECK_LAUNCH();
   return 0;
 }
+B200_POOL_BOTH(b200_colsum_accum, (const void* dy, size_t rows, int C, int c_valid, float* out, void* stream),
+               (dy, rows, C, c_valid, out, stream))

@@ -72,6 +72,20 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// kind::tf32: A and B are fp32 in shared memory, the tensor core uses sign + 8 exponent + 10 mantissa bits of each (K = 8)
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+template <typename T>
+__device__ __forceinline__ void umma(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  if (sizeof(T) == 2) umma_bf16(d_tmem, a_desc, b_desc, idesc, accumulate);
+  else umma_tf32(d_tmem, a_desc, b_desc, idesc, accumulate);
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -100,13 +114,35 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr, uint32_t lbo_b
   d |= (uint64_t)2 << 61;   // SWIZZLE_128B
   return d;
 }
-// Instruction descriptor for kind::f16: bf16 x bf16 -> fp32
-__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+// MN-major operand of 32-bit elements: the only legal form is SWIZZLE_128B_BASE32B (layout type 1): 128-byte rows of 32 MN
+// elements, 4-k-row atoms `sbo_bytes` (512 when packed) apart, 32-byte units XORed with (k-row & 3); `lbo_bytes` between
+// 128-byte MN groups.
+__device__ __forceinline__ uint64_t make_desc_base32(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+  d |= (uint64_t)1 << 46;   // version
+  d |= (uint64_t)1 << 61;   // SWIZZLE_128B_BASE32B
+  return d;
+}
+// MN-major tile whose k-rows are packed 128 B apart: 16-bit elements -> 8-row atoms 1024 B apart, 32-bit -> 4-row atoms 512 B apart
+template <typename T>
+__device__ __forceinline__ uint64_t make_desc_mn(uint32_t smem_addr, uint32_t group_stride_bytes) {
+  return sizeof(T) == 2 ? make_desc(smem_addr, group_stride_bytes, 1024) : make_desc_base32(smem_addr, group_stride_bytes, 512);
+}
+// Instruction descriptor for kind::f16 / kind::tf32 with fp32 accumulation; fmt: A/B format (1 = BF16, 2 = TF32)
+__host__ __device__ constexpr uint32_t make_idesc(int M, int N, int a_mn_major, int b_mn_major, uint32_t fmt = 1) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 __device__ __forceinline__ uint32_t swz(uint32_t row, uint32_t chunk) { return row * 128u + ((chunk ^ (row & 7u)) << 4); }
+// byte offset of 16-byte chunk `chunk` (0..7) of k-row `row` inside one 128-byte-wide MN group of an MN-major tile
+template <typename T>
+__device__ __forceinline__ uint32_t swz_mn(uint32_t row, uint32_t chunk) {
+  return sizeof(T) == 2 ? swz(row, chunk) : row * 128u + ((((chunk >> 1) ^ (row & 3u)) << 5) | ((chunk & 1u) << 4));
+}
 
 // ---- TMA (cp.async.bulk.tensor) -----------------------------------------------------------------
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t tx_bytes) {
