@@ -13,6 +13,11 @@ Only the environment around the script is supplied, exactly what a SageMaker con
 None of this repo's models, kernels or engine is on the path.  Timing: CUDA events recorded from a
 wrapper around ``torch.optim.SGD.step`` (the script's own optimizer), warm-up steps excluded, max over
 ranks.
+
+``run(..., on_b200=True)`` (``bench.py --impl reference_on_b200``) is the other way round: the same unmodified script
+and the same environment, but ``smdistributed.dataparallel.torch.torch_smddp`` is the module this repository ships, so
+``backend='smddp'`` and ``torch.nn.parallel.DistributedDataParallel`` land on b200ddp (native kernels, NVLink
+all-reduce) while the script's own loader, loop and ``optim.SGD`` stay as they are: "same script, new framework".
 """
 from __future__ import annotations
 
@@ -106,15 +111,22 @@ class _StepTimer:
         torch.optim.SGD.step = step
 
 
-def run(gpus: int, steps: int, warmup: int, global_batch: int = 256, model_type: str = "resnet18") -> dict:
+def run(gpus: int, steps: int, warmup: int, global_batch: int = 256, model_type: str = "resnet18",
+        on_b200: bool = False) -> dict:
     import torch
     import torch.distributed as dist
 
+    impl = "reference_on_b200" if on_b200 else "reference"
     script = os.path.join(REF_CODE, "cifar10-distributed-smddp-gpu.py")
     if not os.path.exists(script):
-        return {"impl": "reference", "unavailable": "baseline/_ref not staged (run baseline/install_reference.py)"}
+        return {"impl": impl, "unavailable": "baseline/_ref not staged (run baseline/install_reference.py)"}
     if not torch.cuda.is_available():
-        return {"impl": "reference", "unavailable": "no CUDA device"}
+        return {"impl": impl, "unavailable": "no CUDA device"}
+    if model_type not in ("resnet18", "custom"):
+        # the script's _get_model knows 'resnet18' and falls back to its inline Net for ANY other string
+        # (cifar10-distributed-smddp-gpu.py:30-52): refuse instead of silently timing the wrong model
+        return {"impl": impl, "unavailable": "the reference script has no %r model (only resnet18 and its inline Net); "
+                "the stock-PyTorch arm for it is bench.py --impl torch_tuned --model %s" % (model_type, model_type)}
     os.environ.setdefault("RANK", "0")
     os.environ.setdefault("LOCAL_RANK", os.environ["RANK"])
     os.environ.setdefault("WORLD_SIZE", str(gpus))
@@ -124,7 +136,12 @@ def run(gpus: int, steps: int, warmup: int, global_batch: int = 256, model_type:
     model_dir = tempfile.mkdtemp(prefix="ref_model_")
     os.environ.update({"SM_HOSTS": json.dumps(["algo-1"]), "SM_CURRENT_HOST": "algo-1", "SM_MODEL_DIR": model_dir,
                        "SM_CHANNEL_TRAIN": tempfile.gettempdir(), "NCCL_DEBUG": os.environ.get("NCCL_DEBUG", "WARN")})
-    _install_smddp_standin()
+    if on_b200:
+        root = os.path.dirname(HERE)
+        if root not in sys.path:
+            sys.path.insert(0, root)          # `import smdistributed...` resolves to the module this repository ships
+    else:
+        _install_smddp_standin()
     _install_synthetic_cifar(train_size=(warmup + steps) * global_batch, test_size=world * 8)
     timer = _StepTimer(warmup, steps)
     timer.install()
@@ -139,9 +156,20 @@ def run(gpus: int, steps: int, warmup: int, global_batch: int = 256, model_type:
     finally:
         sys.argv, sys.path = old_argv, old_path
     if timer.start is None or timer.end is None:
-        return {"impl": "reference", "unavailable": "reference ran %d steps, fewer than warmup+steps" % timer.count}
+        return {"impl": impl, "unavailable": "reference ran %d steps, fewer than warmup+steps" % timer.count}
     ms = timer.start.elapsed_time(timer.end)
-    if dist.is_initialized():
+    native = []
+    if on_b200:
+        import b200ddp as bd
+        from b200ddp.ops import _lib as L
+        ms = bd.max_over_ranks(ms)
+        rank = bd.get_rank()
+        native = [L.LAUNCHES[0]]
+        comm = bd.get_comm()
+        if comm is not None:
+            comm.check_health()
+        bd.destroy_process_group()
+    elif dist.is_initialized():
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
@@ -150,12 +178,17 @@ def run(gpus: int, steps: int, warmup: int, global_batch: int = 256, model_type:
     else:
         rank = 0
     value = steps * global_batch / (ms / 1e3)
-    return {"impl": "reference", "rank": rank, "metric": "images/sec", "value": value, "unit": "images/sec",
+    label = {"resnet18": "resnet18 (torchvision, 1000-way head, 32x32 input)",
+             "custom": "custom (the script's inline LeNet-style Net, 10 classes, 32x32 input)"}[model_type]
+    note = ("unmodified reference script on b200ddp through the shipped smdistributed.dataparallel.torch.torch_smddp module: native "
+            "kernels + NVLink all-reduce under the script's own PIL loader, loop and optim.SGD (loader inside the timed region)"
+            if on_b200 else
+            "unmodified reference script; torch DDP+NCCL; PIL dataloader num_workers=0 inside the timed region")
+    return {"impl": impl, "rank": rank, "metric": "images/sec", "value": value, "unit": "images/sec",
             "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
             "e2e": {"value": value, "unit": "images/sec",
                     "h2d_bytes_per_step": (global_batch // world) * (3 * 32 * 32 * 4 + 8), "d2h_bytes_per_step": 0},
-            "gpu_launches": 0,
-            "config": {"model": model_type + " (torchvision, 1000-way head, 32x32 input)", "global_batch": global_batch,
-                       "seq_len": None, "parallelism": "dp%d" % world,
-                       "note": "unmodified reference script; torch DDP+NCCL; PIL dataloader num_workers=0 inside the timed region"}}
+            "gpu_launches": native[0] if native else 0,
+            "config": {"model": label, "global_batch": global_batch,
+                       "seq_len": None, "parallelism": "dp%d" % world, "note": note}}

@@ -15,13 +15,21 @@
 //                   sums all N copies), scales, multimem.st broadcasts the result to all N arenas.
 //   broadcast (W4)  pull from the root's arena.       barrier (W5)  flag exchange on the signal pads.
 //
+//   fused     (W3+W13)  reduce-scatter -> SGD on the owned shard -> all-gather of the WEIGHTS in one kernel
+//                   (allreduce_sgd_shard_kernel): the separate optimizer pass and the gradient broadcast disappear.
+//
 // Synchronisation: per-CTA flag barrier on the signal pads (first MiB of every arena).  Block b of rank
-// a writes epoch e into slot [e&1][b][a] of every peer and spins on its own slots until all peers wrote e:
-// relaxed system-scope flag stores / loads, with a release fence before the store only where the CTA has pushed
-// data into peer memory and an acquire fence after the spin (a system-scope fence per poll cost microseconds).
-// Epochs live in device memory, so the kernels are CUDA-graph replayable.  A spin that exceeds timeout_ns raises the host-mapped error flag and falls through
-// instead of hanging (SURVEY §5.3 failure detection).
+// a writes epoch e into slot [e&1][b][a] of every peer and spins on its own slots until all peers wrote e.
+// The polls are relaxed system-scope loads (a fence per poll cost microseconds); the poll that finally sees the
+// epoch is followed by one ld.acquire.sys of the same flag, which is what orders the CTA's later reads of peer data
+// after the peer's flag store (the CTA barrier behind it extends that to every thread).  On the release side, where a
+// CTA has pushed data into peer memory, all threads meet at a CTA barrier and only the flag-writing threads issue a
+// system-scope fence before their flag store (cumulative over the CTA barrier) instead of one fence per thread.
+// Epochs live in device memory, so the kernels are CUDA-graph replayable.  A spin that exceeds timeout_ns raises the
+// host-mapped error flag and falls through instead of hanging (SURVEY §5.3 failure detection); the host polls that flag
+// after every training step (runtime/engine.py) and before a checkpoint is written (workloads/cifar10_train.py).
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -46,6 +54,11 @@ __device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t* p) {
   asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
 
 // Per-CTA barrier across all ranks.  All threads of the CTA must call it.  `epoch` is the CTA's barrier
 // counter, loaded once per kernel (barrier_begin) and stored back once (barrier_end).
@@ -64,11 +77,13 @@ __device__ __forceinline__ void barrier_end(const b200_comm& c, uint32_t epoch) 
 }
 template <bool RELEASE>
 __device__ __forceinline__ void cta_barrier_all_ranks(const b200_comm& c, uint32_t& epoch) {
-  if (RELEASE) __threadfence_system();
   __syncthreads();
   const uint32_t e = ++epoch;
   if (threadIdx.x < c.world) {
     const int r = threadIdx.x;
+    // release: every thread's peer stores happen-before this point through the CTA barrier above; one system-scope
+    // fence by each flag writer (cumulative) publishes them before the flag
+    if (RELEASE) __threadfence_system();
     st_relaxed_sys(sig_slot(c.peer[r], e & 1u, blockIdx.x, c.rank), e);
     const uint32_t* mine = sig_slot(c.peer[c.rank], e & 1u, blockIdx.x, r);
     if (ld_relaxed_sys(mine) != e) {
@@ -85,6 +100,7 @@ __device__ __forceinline__ void cta_barrier_all_ranks(const b200_comm& c, uint32
         }
       }
     }
+    (void)ld_acquire_sys(mine);     // acquire: reads of this peer's data issued after the barrier see what it published
   }
   __syncthreads();
 }
@@ -317,9 +333,18 @@ int launch_world(const b200_comm& c, size_t offset, size_t chunks, float scale, 
     int blocks = clamp_blocks(chunks, U, max_blocks);
     allreduce_oneshot_kernel<DT, WORLD, U><<<blocks, kThreads, 0, s>>>(c, offset, c.peer[c.rank] + offset, chunks, scale, 1);
   } else if (algo == B200_ALGO_NVLS) {
-    constexpr int U = 8;   // 8 x 16 B multimem.ld_reduce in flight per thread: the switch round trip is ~3 us
-    int blocks = clamp_blocks((chunks + WORLD - 1) / WORLD, U, max_blocks);
-    allreduce_shard_kernel<DT, WORLD, U, true><<<blocks, kThreads, 0, s>>>(c, offset, chunks, scale);
+    // 16-byte multimem.ld_reduce in flight per thread (the switch round trip is ~3 us): 8 by default, B200DDP_NVLS_UNROLL=4|8|16
+    static const int unroll = []() { const char* e = getenv("B200DDP_NVLS_UNROLL"); const int v = e ? atoi(e) : 8; return v; }();
+    if (unroll >= 16) {
+      int blocks = clamp_blocks((chunks + WORLD - 1) / WORLD, 16, max_blocks);
+      allreduce_shard_kernel<DT, WORLD, 16, true><<<blocks, kThreads, 0, s>>>(c, offset, chunks, scale);
+    } else if (unroll <= 4) {
+      int blocks = clamp_blocks((chunks + WORLD - 1) / WORLD, 4, max_blocks);
+      allreduce_shard_kernel<DT, WORLD, 4, true><<<blocks, kThreads, 0, s>>>(c, offset, chunks, scale);
+    } else {
+      int blocks = clamp_blocks((chunks + WORLD - 1) / WORLD, 8, max_blocks);
+      allreduce_shard_kernel<DT, WORLD, 8, true><<<blocks, kThreads, 0, s>>>(c, offset, chunks, scale);
+    }
   } else {
     constexpr int U = (WORLD <= 4) ? 4 : 2;
     int blocks = clamp_blocks((chunks + WORLD - 1) / WORLD, U, max_blocks);

@@ -222,38 +222,35 @@ def test_augment_fp32_matches_reference_transform():
     assert float(got[:, 3:].abs().max()) == 0.0
 
 
-@pytest.mark.parametrize("model_type,batch", [("resnet18", 32), ("resnet18", 8)])
-def test_resnet18_fp32_matches_cpu_oracle(model_type, batch):
-    """Whole-model check at the reference's precision: logits, loss and every parameter gradient of one training
-    forward/backward on the native fp32/TF32 path against the same model evaluated by stock torch on the CPU in fp32."""
+def test_workshop_net_fp32_matches_cpu_oracle():
+    """The workshop Net through the tensor-core layers in fp32/TF32 mode (channel counts padded 3->8, 6->8, 84->88, 10->16):
+    logits, loss and every parameter gradient against stock torch on the CPU.  (resnet18: tests/test_gpu_chain.py.)"""
     import copy
     import b200ddp as bd
     from b200ddp.models import get_model
     from b200ddp.nn import CrossEntropyLoss
-    from b200ddp.ops import native as nv
+    from b200ddp.ops import functional as BF
     dev = _dev()
     torch.manual_seed(11)
     bd.set_compute_dtype("fp32")
+    BF.assume_unit_loss_grad(False)
     try:
-        ref = get_model(model_type)
+        ref = get_model("custom")
         ours = copy.deepcopy(ref).to(dev)
-        x = torch.randn(batch, 3, 32, 32)
-        y = torch.randint(0, 10, (batch,))
+        x = torch.randn(64, 3, 32, 32)
+        y = torch.randint(0, 10, (64,))
         crit = CrossEntropyLoss()
-        ref.train()
-        ours.train()
         lr = crit(ref(x), y)
         lr.backward()
-        nv.SPLIT_K[0] = True
-        lo = crit(ours(x.to(dev)), y.to(dev))
+        out = ours(x.to(dev))
+        assert out.dtype == torch.float32
+        lo = crit(out.contiguous(), y.to(dev))
         lo.backward()
         torch.cuda.synchronize()
-        assert abs(float(lo) - float(lr)) < 2e-2 * (1.0 + abs(float(lr))), (float(lo), float(lr))
-        worst = 0.0
+        assert abs(float(lo) - float(lr)) < 2e-3 * (1.0 + abs(float(lr))), (float(lo), float(lr))
         for (n, p), (_, q) in zip(ours.named_parameters(), ref.named_parameters()):
             assert p.grad is not None, n
             rel = float((p.grad.cpu() - q.grad).norm() / (q.grad.norm() + 1e-12))
-            worst = max(worst, rel)
-            assert rel < 5e-2, "gradient of %s: relative error %.3e" % (n, rel)
+            assert rel < 5e-3, "gradient of %s: relative error %.3e" % (n, rel)
     finally:
         bd.set_compute_dtype("bf16")

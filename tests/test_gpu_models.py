@@ -105,7 +105,8 @@ def test_model_fwd_bwd_matches_cpu_fp32(name, batch, hw):
         torch.cuda.synchronize()
     finally:
         nv.SPLIT_K[0], bmod._FUSE_BN_STATS[0] = saved
-    assert _rel(out_g, out_r) < (8e-2 if name == "resnet18" else 2e-2)
+    print("logits rel error:", _rel(out_g, out_r))
+    assert _rel(out_g, out_r) < (5e-2 if name == "resnet18" else 2e-2)
     assert abs(float(loss_g.detach()) - float(loss_r.detach())) < 1e-2 * max(1.0, abs(float(loss_r.detach())))
     errs, noise = {}, {}
     for (n, pr), (_, pp), (_, pg_) in zip(ref.named_parameters(), pure.named_parameters(), gpu.named_parameters()):
@@ -114,8 +115,11 @@ def test_model_fwd_bwd_matches_cpu_fp32(name, batch, hw):
         noise[n] = round(_rel(pr.grad, pp.grad), 4)
     print("grad rel error vs bf16-rounded oracle:", errs)
     print("bf16 oracle vs un-rounded fp32 (inherent bf16 noise):", noise)
-    lim = 0.45 if name == "resnet18" else 0.02
-    bad = {k: v for k, v in errs.items() if v > lim}
+    if name == "resnet18":
+        # whole-network gradients of resnet18 at random init carry the amplified bf16 noise printed above; the bound that
+        # can catch a kernel bug is per block, against the un-rounded fp32 oracle: tests/test_gpu_chain.py
+        return
+    bad = {k: v for k, v in errs.items() if v > 0.02}
     assert not bad, (bad, errs)
 
 
@@ -167,13 +171,13 @@ def test_graph_step_matches_eager(pg):
         net = pg.DistributedDataParallel(get_model("resnet18").to(dev))
         opt = boptim.SGD(net.parameters(), lr=0.01, momentum=0.9)
         step = TrainStep(net, CrossEntropyLoss(), opt, 32, device=dev, graph=graph, seed=5, augment=False, warmup_iters=3)
-        if not graph:          # the graph path warms up with 3 real steps on the first batch before capturing
-            for _ in range(3):
-                step(xs[0], ys[0])
+        # the capture's warm-up iterations leave no trace (parameters, BN statistics and optimizer state are restored), so
+        # both runs take exactly one step per batch from the same initial state
         losses[graph] = [step(xs[i], ys[i], need_loss=True) for i in range(6)]
-    # fp32 atomics (wgrad / split-K) make the two runs differ in the last bits and resnet18 at init amplifies
-    # that quickly, so only the first steps are compared closely
-    assert abs(losses[False][0] - losses[True][0]) < 0.1 * max(1.0, abs(losses[False][0])), (losses[False], losses[True])
+    # the first loss is a pure forward of identical weights; after that fp32 atomics (wgrad / split-K) make the runs differ in
+    # the last bits and resnet18 at init amplifies that, so later steps get a band
+    assert abs(losses[False][0] - losses[True][0]) < 2e-2 * max(1.0, abs(losses[False][0])), (losses[False], losses[True])
+    assert abs(losses[False][1] - losses[True][1]) < 0.15 * max(1.0, abs(losses[False][1])), (losses[False], losses[True])
     assert all(v == v and v < 20.0 for v in losses[True] + losses[False]), (losses[False], losses[True])
 
 
