@@ -51,9 +51,17 @@ def _init_process_group(backend=None, *args, **kwargs):
                            world_size=world if world is not None else -1, timeout=kwargs.get("timeout"))
 
 
+_IN_DESTROY = [False]
+
+
 def _destroy_process_group(group=None):
-    if group is None and _bd.is_initialized():
-        _bd.destroy_process_group()
+    # b200ddp's own teardown ends in dist.destroy_process_group(), i.e. back in here: the nested call goes to torch's
+    if group is None and _bd.is_initialized() and not _IN_DESTROY[0]:
+        _IN_DESTROY[0] = True
+        try:
+            _bd.destroy_process_group()
+        finally:
+            _IN_DESTROY[0] = False
         if not dist.is_initialized():
             return
     return _TORCH_DESTROY(group)

@@ -55,10 +55,34 @@ def _stages(model):
     return st
 
 
+class _MaskedRelu:
+    """The oracle's ReLUs, replayed with the masks the native stage produced.  An activation within rounding of zero lands
+    on either side of the ReLU depending on the arithmetic; a handful of such flips changes a gradient's Frobenius norm by
+    sqrt(fraction flipped) -- 1.5e-2 for one element in 4000 -- which says nothing about a kernel.  With the oracle using
+    the SAME masks, what is left is the arithmetic error of the kernels."""
+
+    def __init__(self, masks):
+        self.masks, self.i, self.real = masks, 0, F.relu
+
+    def __call__(self, y, inplace=False):
+        m = self.masks[self.i]
+        self.i += 1
+        assert m.shape == y.shape, (m.shape, y.shape)
+        return y * m
+
+    def __enter__(self):
+        F.relu = self
+        return self
+
+    def __exit__(self, *exc):
+        F.relu = self.real
+
+
 # (compute dtype, bound on block outputs / input gradients, bound on parameter gradients)
-@pytest.mark.parametrize("dtype,out_tol,grad_tol", [("fp32", 5e-3, 1e-2), ("bf16", 2e-2, 5e-2)])
+@pytest.mark.parametrize("dtype,out_tol,grad_tol", [("fp32", 2e-3, 5e-3), ("bf16", 2e-2, 3e-2)])
 def test_resnet18_blocks_chained(dtype, out_tol, grad_tol):
     import b200ddp as bd
+    from b200ddp import nn as bnn
     from b200ddp.models import get_model
     from b200ddp.ops import functional as BF
     dev = _dev()
@@ -71,41 +95,50 @@ def test_resnet18_blocks_chained(dtype, out_tol, grad_tol):
     x = torch.randn(batch, 3, 32, 32)
     y = torch.randint(0, 1000, (batch,))
 
-    # ---- oracle pass: record every stage's input, output and output gradient
-    rec = []
-    h = x
-    for name, stage in _stages(ref):
-        inp = h.detach().clone().requires_grad_(True)
-        out = stage(inp)
-        rec.append({"name": name, "inp": inp, "out": out})
-        h = out
-    loss = F.cross_entropy(rec[-1]["out"], y)
-    g = torch.autograd.grad(loss, rec[-1]["out"])[0]
-    for r in reversed(rec):                     # stage-local backward: the grad of a stage's input feeds the one before it
-        r["gout"] = g
-        r["out"].backward(g)
-        g = r["inp"].grad
-    ref_grads = {n: p.grad.clone() for n, p in ref.named_parameters()}
-
-    # ---- native stages, each fed the oracle's tensors
     bd.set_compute_dtype(dtype)
     BF.assume_unit_loss_grad(False)
     report, bad = {}, {}
     try:
-        for (name, stage), r in zip(_stages(ours), rec):
-            inp = r["inp"].detach().to(dev).requires_grad_(name != "stem")
-            out = stage(inp)
-            e_out = _rel(out, r["out"])
-            out.float().backward(r["gout"].to(dev))
+        # ---- forward, stage by stage: the native stage runs on the ORACLE's input, then the oracle runs with its masks
+        rec = []
+        h = x
+        for (name, stage_o), (_, stage_n) in zip(_stages(ref), _stages(ours)):
+            masks, hooks = [], []
+            for m in stage_n.modules():
+                if isinstance(m, bnn.BatchNorm2d) and m.fused_relu:
+                    hooks.append(m.register_forward_hook(lambda mod, i, o: masks.append((o.detach() > 0).float().cpu())))
+            n_inp = h.detach().to(dev).requires_grad_(name != "stem")
+            n_out = stage_n(n_inp)
             torch.cuda.synchronize()
-            errs = {"out": e_out}
+            for hk in hooks:
+                hk.remove()
+            o_inp = h.detach().clone().requires_grad_(True)
+            with _MaskedRelu(masks) as mr:
+                o_out = stage_o(o_inp)
+            assert mr.i == len(masks), (name, mr.i, len(masks))
+            rec.append({"name": name, "o_inp": o_inp, "o_out": o_out, "n_inp": n_inp, "n_out": n_out, "stage_n": stage_n})
+            h = o_out
+        # ---- oracle backward, stage-local: the gradient of a stage's input feeds the stage before it
+        loss = F.cross_entropy(rec[-1]["o_out"], y)
+        g = torch.autograd.grad(loss, rec[-1]["o_out"])[0]
+        for r in reversed(rec):
+            r["gout"] = g
+            r["o_out"].backward(g)
+            g = r["o_inp"].grad
+        ref_grads = {n: p.grad.clone() for n, p in ref.named_parameters()}
+        # ---- native backward of every stage from the ORACLE's output gradient
+        for r in rec:
+            name = r["name"]
+            errs = {"out": _rel(r["n_out"], r["o_out"])}
+            r["n_out"].float().backward(r["gout"].to(dev))
+            torch.cuda.synchronize()
             if name != "stem":
-                errs["dinp"] = _rel(inp.grad, r["inp"].grad)
-            if e_out > out_tol:
-                bad[name + ".out"] = e_out
-            if errs.get("dinp", 0.0) > out_tol * 2:
+                errs["dinp"] = _rel(r["n_inp"].grad, r["o_inp"].grad)
+            if errs["out"] > out_tol:
+                bad[name + ".out"] = errs["out"]
+            if errs.get("dinp", 0.0) > grad_tol:
                 bad[name + ".dinp"] = errs["dinp"]
-            for pn, p in stage.named_parameters():
+            for pn, p in r["stage_n"].named_parameters():
                 full = pn if name in ("stem", "head") else name + "." + pn
                 assert p.grad is not None, full
                 e = _rel(p.grad, ref_grads[full])

@@ -57,10 +57,16 @@ def test_resnet18_trains_like_torch_fp32():
     from b200ddp.runtime.engine import TrainStep
     from b200ddp.utils.data import SyntheticCIFAR10
     dev = _dev()
-    train = SyntheticCIFAR10(train=True, size=STEPS * BATCH)
-    test = SyntheticCIFAR10(train=False, size=2000)
+    # heavy pixel noise, and a quarter of the TRAINING labels re-drawn at random: the loss cannot collapse to zero in the
+    # first window, so all six windows carry information (the held-out labels stay clean)
+    train = SyntheticCIFAR10(train=True, size=STEPS * BATCH, noise=120.0)
+    test = SyntheticCIFAR10(train=False, size=2000, noise=120.0)
+    g = torch.Generator().manual_seed(99)
+    labels = torch.from_numpy(train.targets).clone()
+    flip = torch.rand(labels.shape[0], generator=g) < 0.25
+    labels[flip] = torch.randint(0, 10, (int(flip.sum()),), generator=g)
     xs = torch.from_numpy(train.data).view(STEPS, BATCH, 32, 32, 3)
-    ys = torch.from_numpy(train.targets).view(STEPS, BATCH)
+    ys = labels.view(STEPS, BATCH)
     tx, ty = torch.from_numpy(test.data), torch.from_numpy(test.targets)
 
     torch.manual_seed(5)
@@ -111,7 +117,7 @@ def test_resnet18_trains_like_torch_fp32():
     print("oracle fp32 windows", [round(v, 3) for v in ref_w], "acc", ref_acc)
     for dtype, (w, acc) in results.items():
         print(dtype, "windows", [round(v, 3) for v in w], "acc", acc)
-    assert ref_w[-1] < 0.5 * ref_w[0] and ref_acc > 0.9, "the oracle itself did not learn the synthetic set"
+    assert ref_w[-1] < 0.7 * ref_w[0] and ref_acc > 0.8, "the oracle itself did not learn the synthetic set"
     for dtype, (w, acc) in results.items():
         band = 0.10 if dtype == "fp32" else 0.15
         for k, (a, b) in enumerate(zip(w, ref_w)):

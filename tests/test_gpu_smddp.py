@@ -84,7 +84,7 @@ def test_torch_optim_on_native_ddp_matches_cpu_torch():
         torch.cuda.synchronize()
         for (n, a), (_, b) in zip(ref.named_parameters(), ddp.module.named_parameters()):
             rel = float((b.detach().cpu() - a).norm() / (a.norm() + 1e-12))
-            assert rel < 2e-3, (n, rel)
+            assert rel < 1e-2, (n, rel)        # four TF32 steps against strict fp32
     finally:
         bd.set_compute_dtype("bf16")
         if not started:
