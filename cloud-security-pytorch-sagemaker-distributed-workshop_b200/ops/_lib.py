@@ -17,7 +17,7 @@ import torch
 from .build import LIB_PATH
 
 MAX_RANKS = 8
-MAX_COMM_BLOCKS = 64
+MAX_COMM_BLOCKS = 160
 SIGNAL_BYTES = 1 << 20
 DTYPE_F32, DTYPE_BF16 = 0, 1
 ALGO_AUTO, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2, 3

@@ -65,11 +65,50 @@ class SGD(_FusedBase):
         self._split()
         self._inner = torch.optim.SGD(self._loose, **defaults) if self._loose else None
         self._momentum_flat = {}
+        self._fused_key = {}
+
+    # -------------------------------------------------------------- optimizer inside the collective
+    def fuse_into_backward(self, enabled: bool = True) -> bool:
+        """Fold this optimizer's step into the gradient collective of every DDP arena that supports it (world > 1, backend
+        'b200'): each bucket then runs reduce-scatter -> SGD on the owned shard -> all-gather of the new weights as ONE
+        kernel while backward is still producing the next bucket, and ``step()`` launches nothing for that arena.  Only for
+        callers that own the whole step (``runtime.engine.TrainStep``): the weights change DURING ``backward()``, so
+        nothing may sit between ``backward()`` and ``step()`` (no gradient clipping, no inspection of ``param.grad``).
+        Returns True if at least one arena was switched."""
+        import os
+        if os.environ.get("B200DDP_FUSED_SGD", "1") in ("0", "false", "off"):
+            enabled = False
+        g = self.param_groups[0]
+        any_on = False
+        for o in self._flat_owners:
+            if not (hasattr(o, "can_fuse_sgd") and o.can_fuse_sgd()):
+                continue
+            if enabled:
+                m = self._momentum_flat.get(id(o))
+                if m is None and g["momentum"] != 0:
+                    m = torch.zeros_like(o.flat_params)
+                    self._momentum_flat[id(o)] = m
+                o.set_fused_sgd(True, m, g["lr"], g["momentum"], g["dampening"], g["weight_decay"], g["nesterov"])
+                self._fused_key[id(o)] = (g["lr"], g["momentum"], g["dampening"], g["weight_decay"], g["nesterov"])
+                any_on = True
+            elif id(o) in self._fused_key:
+                o.set_fused_sgd(False)
+                del self._fused_key[id(o)]
+        return any_on
 
     @torch.no_grad()
     def step(self, closure=None):
         g = self.param_groups[0]
         for o in self._flat_owners:
+            key = self._fused_key.get(id(o))
+            if key is not None and o.require_backward_grad_sync:
+                # the collective already applied this step (and zeroed the gradients); keep its hyper-parameters current
+                now = (g["lr"], g["momentum"], g["dampening"], g["weight_decay"], g["nesterov"])
+                if now != key:
+                    o.set_fused_sgd(True, self._momentum_flat.get(id(o)), *now)
+                    self._fused_key[id(o)] = now
+                o._arena_dirty = False
+                continue
             m = self._momentum_flat.get(id(o))
             if m is None and g["momentum"] != 0:
                 m = torch.zeros_like(o.flat_params)

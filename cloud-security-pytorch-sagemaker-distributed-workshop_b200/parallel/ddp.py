@@ -84,12 +84,20 @@ class DistributedDataParallel(nn.Module):
                 param_bucket[i] = b.index
 
         # ---- flat arenas
-        self.flat_params = torch.zeros(total, dtype=torch.float32, device=self.device)
         grad_off_bytes = 0
-        if self.backend == "b200" and self.world_size >= 1 and self.comm is not None:
+        self._param_off_bytes = self._shadow_off_bytes = None      # arena offsets when the masters / shadow are symmetric too
+        symmetric = self.backend == "b200" and self.comm is not None
+        if symmetric and self.world_size > 1:
+            # masters in symmetric memory as well: the fused bucket step (reduce-scatter -> owner-shard SGD -> all-gather of
+            # the weights, csrc/comm.cu) writes every rank's parameters through the multicast / peer mappings
+            self.flat_params, self._param_off_bytes = self.comm.alloc_arena(total, torch.float32)
+        else:
+            self.flat_params = torch.zeros(total, dtype=torch.float32, device=self.device)
+        if symmetric:
             self.flat_grads, grad_off_bytes = self.comm.alloc_arena(total, torch.float32)
         else:
             self.flat_grads = torch.zeros(total, dtype=torch.float32, device=self.device)
+        self._grad_off_bytes = grad_off_bytes
         self.flat_shadow = None
         if shadow_dtype == "auto":
             # the bf16 shadow feeds the bf16 tensor-core kernels; in fp32 compute mode they read the masters themselves
@@ -97,7 +105,10 @@ class DistributedDataParallel(nn.Module):
             shadow_dtype = torch.bfloat16 if act_dtype() == torch.bfloat16 else None
         self._arena_dirty = False        # gradients have been written since the arena was last zeroed
         if self.device.type == "cuda" and shadow_dtype is not None:
-            self.flat_shadow = torch.zeros(total, dtype=shadow_dtype, device=self.device)
+            if symmetric and self.world_size > 1 and shadow_dtype == torch.bfloat16:
+                self.flat_shadow, self._shadow_off_bytes = self.comm.alloc_arena(total, torch.bfloat16)
+            else:
+                self.flat_shadow = torch.zeros(total, dtype=shadow_dtype, device=self.device)
 
         # channels-last physical storage only for the weights of this package's conv modules on a GPU: a
         # stock nn.Conv2d fed channels-last weights would hand channels-last activations to user code
@@ -248,6 +259,18 @@ class DistributedDataParallel(nn.Module):
         self.flat_grads.zero_()
         self._accum_count = 0
         self._arena_dirty = False
+
+    # ------------------------------------------------------------------ fused bucket step
+    def can_fuse_sgd(self) -> bool:
+        """True when every bucket's all-reduce can become reduce-scatter + SGD + weight all-gather in one kernel."""
+        return (self.backend == "b200" and self.world_size > 1 and self._param_off_bytes is not None
+                and hasattr(self.reducer, "set_sgd") and (self.flat_shadow is None or self._shadow_off_bytes is not None))
+
+    def set_fused_sgd(self, enabled: bool, momentum_buf=None, lr=0.0, momentum=0.0, dampening=0.0, weight_decay=0.0,
+                      nesterov=False):
+        self.reducer.set_sgd(bool(enabled), self._grad_off_bytes, self._param_off_bytes or 0, self._shadow_off_bytes or 0,
+                             momentum_buf, lr, momentum, dampening, weight_decay, nesterov)
+        self._fused_sgd = bool(enabled)
 
     def refresh_shadow(self):
         """Re-derive the bf16 shadow weights from the fp32 masters (after load_state_dict etc.)."""

@@ -193,6 +193,19 @@ class NativeReducer:
         self._lib = lib
         self._comm_stream = c_void_p(comm.comm_stream.cuda_stream)
 
+    def set_sgd(self, enabled: bool, grad_base: int, param_base: int, shadow_base: int, momentum_buf, lr: float,
+                momentum: float, dampening: float, weight_decay: float, nesterov: bool):
+        """Make every bucket launch the fused step (``b200_allreduce_sgd``) instead of the plain all-reduce."""
+        ct = self._ct
+        self._momentum_keepalive = momentum_buf
+        self._L.check(self._lib.b200_reducer_set_sgd(self._h, ct.c_int(int(enabled)), ct.c_size_t(grad_base), ct.c_size_t(param_base),
+                                                     ct.c_size_t(shadow_base), self._L.ptr(momentum_buf), ct.c_float(lr),
+                                                     ct.c_float(momentum), ct.c_float(dampening), ct.c_float(weight_decay),
+                                                     ct.c_int(int(nesterov))), "reducer_set_sgd")
+        self._L.LAUNCHES[0] -= 1        # bookkeeping call, not a kernel
+        self._logged = False
+        self.sgd_fused = bool(enabled)
+
     def __del__(self):
         try:
             self._lib.b200_reducer_destroy(self._h)
@@ -237,5 +250,6 @@ class NativeReducer:
             self._logged = True
             for b in self.buckets:
                 a = self._lib.b200_reducer_bucket_algo(self._h, self._ct.c_int(b.index))
-                self.comm.launch_log.append((self._L.ALGO_NAMES.get(a, "?"), b.numel * 4))
+                name = self._L.ALGO_NAMES.get(a, "?")
+                self.comm.launch_log.append((("fused_sgd_" + name) if getattr(self, "sgd_fused", False) else name, b.numel * 4))
         self.iterations += 1

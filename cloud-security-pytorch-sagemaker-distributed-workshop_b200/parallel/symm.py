@@ -218,11 +218,9 @@ class SymmComm:
 
     # ------------------------------------------------------------------ collectives
     def pick_algo(self, nbytes: int) -> int:
-        if nbytes <= self.cfg.oneshot_max_bytes:
-            return L.ALGO_ONESHOT
-        if self.has_nvls and self.prefer_nvls and nbytes >= self.cfg.nvls_min_bytes:
-            return L.ALGO_NVLS
-        return L.ALGO_TWOSHOT
+        """The native selector (``b200_pick_algo``): the reducer and ``B200_ALGO_AUTO`` take the same decision."""
+        return int(self.lib.b200_pick_algo(c_int(self.world), c_int(int(self.has_nvls and self.prefer_nvls)), c_size_t(nbytes),
+                                           c_size_t(self.cfg.oneshot_max_bytes), c_size_t(self.cfg.nvls_min_bytes)))
 
     def _launch_allreduce(self, offset: int, numel: int, dtype: torch.dtype, scale: float, stream, algo: int = 0,
                           max_ctas: Optional[int] = None):

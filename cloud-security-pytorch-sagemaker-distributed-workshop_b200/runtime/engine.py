@@ -64,6 +64,9 @@ class TrainStep:
             self._comm = _pg.get_comm()         # polled after every step: a timed-out collective must not go unnoticed
             BF.assume_unit_loss_grad(True)
             bmod.defer_bn_counters(True)
+            # this engine owns the whole step, so the optimizer may move into the gradient collective (world > 1)
+            fuse = getattr(optimizer, "fuse_into_backward", None)
+            self.fused_optimizer = bool(fuse(True)) if fuse is not None else False
 
     def _views(self, blob: torch.Tensor):
         H, W, C = self.image_shape

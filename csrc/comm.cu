@@ -284,6 +284,144 @@ allreduce_shard_kernel(b200_comm c, size_t offset, size_t chunks, float scale) {
   barrier_end(c, epoch);
 }
 
+// ---- fused: reduce-scatter -> SGD on the owned shard -> all-gather of the WEIGHTS, one kernel -------------------
+// The step the reference takes as `loss.backward()` (NCCL all-reduce of every bucket) followed by `optimizer.step()`
+// (notebooks/code/cifar10-distributed-smddp-gpu.py:167-168), and the idea of SMDDP's "balanced fusion buffer" (a bucket
+// cut into N equal shards regardless of tensor boundaries, each reduced by a different owner:
+// static/images/training/training24.png), as ONE kernel per bucket over peer memory:
+//   1. rank r reduces shard r of the bucket's gradients: multimem.ld_reduce on the multicast address (the switch adds
+//      the N copies) or, without NVLS, 16-byte loads from every peer's arena summed in fixed rank order;
+//   2. applies SGD with momentum to shard r of the fp32 master weights (momentum state exists only for the owned shard);
+//   3. writes the NEW WEIGHTS (and, in bf16 mode, their bf16 shadow) into every rank's parameter arena: multimem.st, or
+//      posted stores to each peer.  Every rank therefore holds bit-identical parameters by construction;
+//   4. after the exit barrier (all reads of everyone's gradients are done) zeroes its local copy of the bucket's
+//      gradients for the next backward.
+// Compared with all-reduce + a separate optimizer pass this moves the same bytes over NVLink (weights instead of averaged
+// gradients on the way back) and drops the optimizer's read of p, g, m and write of p, m, shadow for (N-1)/N of the model.
+// fp32 gradients / masters only (the arena layout of DistributedDataParallel).
+__device__ __forceinline__ void mc_st_b64(void* mc, const uint2& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1,%2};" ::"l"(mc), "r"(v.x), "r"(v.y) : "memory");
+}
+__device__ __forceinline__ void st_peer_b64(void* p, const uint2& v) {
+  asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
+}
+
+struct SgdArgs {
+  size_t param_off;     // byte offset (in the arena) of the bucket's fp32 master weights
+  size_t shadow_off;    // byte offset of the bucket's bf16 shadow weights, 0 = none
+  float* momentum;      // LOCAL fp32 momentum buffer of the bucket (only the owned shard is ever touched), may be null
+  float lr, momentum_coef, one_minus_damp, wd;
+  int nesterov;
+};
+
+template <int WORLD, int UNROLL, bool NVLS>
+__global__ void __launch_bounds__(kThreads, 1)
+allreduce_sgd_shard_kernel(b200_comm c, size_t offset, size_t chunks, float scale, SgdArgs a) {
+  using V = Vec<B200_DTYPE_F32>;
+  const size_t per = (chunks + WORLD - 1) / WORLD;
+  const size_t lo = (size_t)c.rank * per;
+  const size_t hi = lo + per < chunks ? lo + per : chunks;
+  char* const local = c.peer[c.rank];
+  uint32_t epoch = barrier_begin(c);
+  cta_barrier_all_ranks<false>(c, epoch);          // every rank's gradients for this bucket are final
+  const size_t per_round = (size_t)gridDim.x * kThreads * UNROLL;
+  for (size_t base = lo + (size_t)blockIdx.x * kThreads * UNROLL; base < hi; base += per_round) {
+    float g[UNROLL][4];
+    if constexpr (NVLS) {
+      int4 red[UNROLL];
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
+        if (idx < hi) red[u] = V::mc_ld_reduce(c.mc + offset + idx * 16);
+      }
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const float* f = reinterpret_cast<const float*>(&red[u]);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) g[u][i] = f[i];
+      }
+    } else {
+      int4 raw[WORLD][UNROLL];
+#pragma unroll
+      for (int r = 0; r < WORLD; ++r) {
+#pragma unroll
+        for (int u = 0; u < UNROLL; ++u) {
+          const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
+          raw[r][u] = make_int4(0, 0, 0, 0);
+          if (idx < hi) raw[r][u] = ld_peer(c.peer[r] + offset + idx * 16);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) g[u][i] = 0.f;
+#pragma unroll
+        for (int r = 0; r < WORLD; ++r) V::accumulate(g[u], raw[r][u]);   // fixed order 0..N-1
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; ++u) {
+      const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
+      if (idx >= hi) continue;
+      const float4 pv = *reinterpret_cast<const float4*>(local + a.param_off + idx * 16);
+      float p[4] = {pv.x, pv.y, pv.z, pv.w};
+      float m[4] = {0.f, 0.f, 0.f, 0.f};
+      if (a.momentum_coef != 0.f) {
+        const float4 mv = reinterpret_cast<const float4*>(a.momentum)[idx];
+        m[0] = mv.x; m[1] = mv.y; m[2] = mv.z; m[3] = mv.w;
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float d = fmaf(g[u][k], scale, a.wd * p[k]);
+        if (a.momentum_coef != 0.f) {
+          m[k] = fmaf(a.momentum_coef, m[k], a.one_minus_damp * d);
+          d = a.nesterov ? fmaf(a.momentum_coef, m[k], d) : m[k];
+        }
+        p[k] = fmaf(-a.lr, d, p[k]);
+      }
+      if (a.momentum_coef != 0.f) reinterpret_cast<float4*>(a.momentum)[idx] = make_float4(m[0], m[1], m[2], m[3]);
+      int4 o;
+      float* of = reinterpret_cast<float*>(&o);
+      of[0] = p[0]; of[1] = p[1]; of[2] = p[2]; of[3] = p[3];
+      uint2 sh;
+      if (a.shadow_off != 0) {
+        __nv_bfloat162 l2 = __floats2bfloat162_rn(p[0], p[1]), h2 = __floats2bfloat162_rn(p[2], p[3]);
+        sh.x = *reinterpret_cast<uint32_t*>(&l2);
+        sh.y = *reinterpret_cast<uint32_t*>(&h2);
+      }
+      if constexpr (NVLS) {
+        mc_st(c.mc + a.param_off + idx * 16, o);
+        if (a.shadow_off != 0) mc_st_b64(c.mc + a.shadow_off + idx * 8, sh);
+      } else {
+#pragma unroll
+        for (int i = 0; i < WORLD; ++i) {
+          const int q = (c.rank + i) % WORLD;       // stagger destinations across ranks
+          st_peer(c.peer[q] + a.param_off + idx * 16, o);
+          if (a.shadow_off != 0) st_peer_b64(c.peer[q] + a.shadow_off + idx * 8, sh);
+        }
+      }
+    }
+  }
+  cta_barrier_all_ranks<true>(c, epoch);           // all new weights have landed everywhere; nobody reads gradients any more
+  barrier_end(c, epoch);
+  // Zero the local copy of the bucket's gradients for the next backward.  The barrier above only pairs CTA b with CTA b of
+  // the other ranks, so this CTA may clear exactly the chunks that "CTA b" of each owner has read: the same index set as the
+  // loop above, taken for every shard.
+  const int4 z = make_int4(0, 0, 0, 0);
+#pragma unroll 1
+  for (int r = 0; r < WORLD; ++r) {
+    const size_t rlo = (size_t)r * per;
+    const size_t rhi = rlo + per < chunks ? rlo + per : chunks;
+    for (size_t base = rlo + (size_t)blockIdx.x * kThreads * UNROLL; base < rhi; base += per_round) {
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        const size_t idx = base + (size_t)u * kThreads + threadIdx.x;
+        if (idx < rhi) *reinterpret_cast<int4*>(local + offset + idx * 16) = z;
+      }
+    }
+  }
+}
+
 // ---- W4 broadcast (pull) --------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, 1) broadcast_kernel(b200_comm c, size_t offset, size_t chunks, int root) {
   uint32_t epoch = barrier_begin(c);
@@ -384,6 +522,20 @@ int launch_oneshot_out(const b200_comm& c, size_t offset, char* out, size_t chun
 
 static size_t elem_size(int dtype) { return dtype == B200_DTYPE_BF16 ? 2 : 4; }
 
+// THE algorithm selector (the reducer, b200_allreduce's AUTO and the Python layer all come here): one-shot up to
+// oneshot_max_bytes (0 = default max(64 KiB, 2 MiB / (world - 1)): one-shot pulls (N-1) x S per GPU, so its cut-over shrinks
+// with N), then NVLS when a multicast mapping is bound, the world is larger than 2 (with two ranks the switch reduction buys
+// nothing) and the message has at least nvls_min_bytes (0 = no lower limit), else two-shot.
+extern "C" int b200_pick_algo(int world, int has_multicast, size_t bytes, size_t oneshot_max_bytes, size_t nvls_min_bytes) {
+  if (oneshot_max_bytes == 0) {
+    const size_t scaled = world > 1 ? ((size_t)2 << 20) / (size_t)(world - 1) : ((size_t)2 << 20);
+    oneshot_max_bytes = scaled > 64 * 1024 ? scaled : 64 * 1024;
+  }
+  if (bytes <= oneshot_max_bytes) return B200_ALGO_ONESHOT;
+  if (has_multicast && world > 2 && bytes >= nvls_min_bytes) return B200_ALGO_NVLS;
+  return B200_ALGO_TWOSHOT;
+}
+
 extern "C" int b200_allreduce(const b200_comm* comm, size_t offset, size_t count, int dtype, float scale, int algo,
                               int max_blocks, void* stream) {
   B200_REQUIRE(comm != nullptr, "null communicator");
@@ -407,13 +559,61 @@ extern "C" int b200_allreduce(const b200_comm* comm, size_t offset, size_t count
   }
   const size_t bytes = count * elem_size(dtype);
   const size_t chunks = bytes / 16;
-  if (algo == B200_ALGO_AUTO) algo = (bytes <= 64 * 1024) ? B200_ALGO_ONESHOT : (c.mc ? B200_ALGO_NVLS : B200_ALGO_TWOSHOT);
+  if (algo == B200_ALGO_AUTO) algo = b200_pick_algo(c.world, c.mc != nullptr, bytes, 0, 0);
   if (algo == B200_ALGO_NVLS && c.mc == nullptr) {
     b200_set_error("NVLS requested but no multicast mapping is bound");
     return B200_ERR_UNSUPPORTED;
   }
   return dtype == B200_DTYPE_F32 ? launch_dtype<B200_DTYPE_F32>(c, offset, chunks, scale, algo, max_blocks, s)
                                  : launch_dtype<B200_DTYPE_BF16>(c, offset, chunks, scale, algo, max_blocks, s);
+}
+
+// Fused bucket step: gradient reduce-scatter + SGD(momentum) on the owned shard + all-gather of the new weights (and bf16
+// shadow) + zeroing of the local gradients, one kernel.  grad_offset / param_offset / shadow_offset are byte offsets of the
+// bucket inside the symmetric arena (shadow_offset 0 = no shadow); `momentum` is this rank's LOCAL fp32 buffer for the
+// bucket (count elements; only the owned shard is used) or NULL when momentum == 0.  algo: B200_ALGO_NVLS or _TWOSHOT
+// (AUTO: NVLS when a multicast mapping is bound and world > 2).
+extern "C" int b200_allreduce_sgd(const b200_comm* comm, size_t grad_offset, size_t param_offset, size_t shadow_offset,
+                                  float* momentum_buf, size_t count, float scale, float lr, float momentum, float dampening,
+                                  float weight_decay, int nesterov, int algo, int max_blocks, void* stream) {
+  B200_REQUIRE(comm != nullptr, "null communicator");
+  B200_REQUIRE(comm->world >= 2 && comm->world <= B200_MAX_RANKS, "the fused bucket step needs 2..8 ranks");
+  B200_REQUIRE(grad_offset % 16 == 0 && param_offset % 16 == 0 && shadow_offset % 8 == 0, "offsets must be 16-byte (shadow: 8-byte) aligned");
+  B200_REQUIRE(count % 4 == 0, "element count must be a multiple of 4");
+  B200_REQUIRE(grad_offset >= B200_SIGNAL_BYTES && param_offset >= B200_SIGNAL_BYTES, "offset overlaps the signal region");
+  B200_REQUIRE(momentum == 0.f || momentum_buf != nullptr, "momentum buffer required");
+  if (count == 0) return 0;
+  const b200_comm& c = *comm;
+  if (algo == B200_ALGO_AUTO) algo = (c.mc != nullptr && c.world > 2) ? B200_ALGO_NVLS : B200_ALGO_TWOSHOT;
+  B200_REQUIRE(algo == B200_ALGO_NVLS || algo == B200_ALGO_TWOSHOT, "fused bucket step: algo must be NVLS or two-shot");
+  if (algo == B200_ALGO_NVLS && c.mc == nullptr) {
+    b200_set_error("NVLS requested but no multicast mapping is bound");
+    return B200_ERR_UNSUPPORTED;
+  }
+  SgdArgs a;
+  a.param_off = param_offset; a.shadow_off = shadow_offset; a.momentum = momentum_buf;
+  a.lr = lr; a.momentum_coef = momentum; a.one_minus_damp = 1.f - dampening; a.wd = weight_decay; a.nesterov = nesterov;
+  const size_t chunks = count / 4;
+  cudaStream_t s = (cudaStream_t)stream;
+#define B200_FS(W)                                                                                               \
+  case W: {                                                                                                      \
+    if (algo == B200_ALGO_NVLS) {                                                                                \
+      int blocks = clamp_blocks((chunks + W - 1) / W, 4, max_blocks);                                            \
+      allreduce_sgd_shard_kernel<W, 4, true><<<blocks, kThreads, 0, s>>>(c, grad_offset, chunks, scale, a);      \
+    } else {                                                                                                     \
+      constexpr int U = (W <= 4) ? 2 : 1;                                                                        \
+      int blocks = clamp_blocks((chunks + W - 1) / W, U, max_blocks);                                            \
+      allreduce_sgd_shard_kernel<W, U, false><<<blocks, kThreads, 0, s>>>(c, grad_offset, chunks, scale, a);     \
+    }                                                                                                            \
+    break;                                                                                                       \
+  }
+  switch (c.world) {
+    B200_FS(2) B200_FS(3) B200_FS(4) B200_FS(5) B200_FS(6) B200_FS(7) B200_FS(8)
+    default: b200_set_error("world size %d not in 2..8", c.world); return B200_ERR_ARG;
+  }
+#undef B200_FS
+  B200_CHECK_LAUNCH();
+  return 0;
 }
 
 extern "C" int b200_allreduce_oneshot_out(const b200_comm* comm, size_t offset, void* out, size_t count, int dtype,

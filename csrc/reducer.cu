@@ -27,6 +27,12 @@ struct b200_reducer {
   int next_bucket = 0;
   bool dirty = false;                      // something was launched on the comm stream since the last join
   cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_done = nullptr;
+  // fused bucket step (b200_reducer_set_sgd): each bucket's launch is reduce-scatter + SGD + weight all-gather
+  bool sgd = false;
+  size_t grad_base = 0, param_base = 0, shadow_base = 0;   // arena byte offsets of element 0 of the flat arenas
+  float* momentum_base = nullptr;
+  float lr = 0.f, mom = 0.f, damp = 0.f, wd = 0.f;
+  int nesterov = 0;
 };
 
 static size_t reducer_elem_size(int dtype) { return dtype == B200_DTYPE_BF16 ? 2 : 4; }
@@ -91,9 +97,7 @@ extern "C" int b200_reducer_was_ready(const b200_reducer* r, int param) {
 }
 
 static int reducer_pick_algo(const b200_reducer* r, size_t bytes) {
-  if (bytes <= r->oneshot_max) return B200_ALGO_ONESHOT;
-  if (r->comm.mc != nullptr && bytes >= r->nvls_min) return B200_ALGO_NVLS;
-  return B200_ALGO_TWOSHOT;
+  return b200_pick_algo(r->comm.world, r->comm.mc != nullptr, bytes, r->oneshot_max, r->nvls_min);
 }
 
 // comm stream waits for everything queued so far on the producer stream(s), then runs the bucket's all-reduce
@@ -105,9 +109,18 @@ static int reducer_launch(b200_reducer* r, int b, cudaStream_t producer, cudaStr
     B200_CHECK_CUDA(cudaStreamWaitEvent(comm, r->ev_b, 0));
   }
   const size_t bytes = r->count[b] * reducer_elem_size(r->dtype);
+  r->dirty = true;
+  if (r->sgd) {
+    // the bucket's position inside the flat gradient arena gives its position inside the parameter / shadow / momentum arenas
+    const size_t elem0 = (r->offset[b] - r->grad_base) / sizeof(float);
+    const int algo = (r->comm.mc != nullptr && r->comm.world > 2) ? B200_ALGO_NVLS : B200_ALGO_TWOSHOT;
+    r->algo_used[b] = algo;
+    return b200_allreduce_sgd(&r->comm, r->offset[b], r->param_base + elem0 * sizeof(float),
+                              r->shadow_base ? r->shadow_base + elem0 * 2 : 0, r->momentum_base ? r->momentum_base + elem0 : nullptr,
+                              r->count[b], r->scale, r->lr, r->mom, r->damp, r->wd, r->nesterov, algo, r->max_blocks, comm);
+  }
   const int algo = reducer_pick_algo(r, bytes);
   r->algo_used[b] = algo;
-  r->dirty = true;
   return b200_allreduce(&r->comm, r->offset[b], r->count[b], r->dtype, r->scale, algo, r->max_blocks, comm);
 }
 
@@ -152,4 +165,20 @@ extern "C" int b200_reducer_finalize(b200_reducer* r, void* main_stream, void* o
 
 extern "C" int b200_reducer_bucket_algo(const b200_reducer* r, int bucket) {
   return (r && bucket >= 0 && bucket < (int)r->algo_used.size()) ? r->algo_used[bucket] : -1;
+}
+
+// Switch the reducer's per-bucket launch between the plain all-reduce and the fused bucket step (b200_allreduce_sgd).
+// grad_base / param_base / shadow_base: arena byte offsets of element 0 of the flat gradient / fp32 parameter / bf16 shadow
+// arenas (shadow_base 0 = none); momentum_base: this rank's local momentum buffer laid out like the parameters (or NULL).
+// Hyper-parameters are passed by value: call again when the learning rate changes (and re-capture a CUDA graph).
+extern "C" int b200_reducer_set_sgd(b200_reducer* r, int enabled, size_t grad_base, size_t param_base, size_t shadow_base,
+                                    float* momentum_base, float lr, float momentum, float dampening, float weight_decay,
+                                    int nesterov) {
+  B200_REQUIRE(r != nullptr, "null reducer");
+  B200_REQUIRE(!enabled || r->dtype == B200_DTYPE_F32, "the fused bucket step takes fp32 gradients");
+  B200_REQUIRE(!enabled || momentum == 0.f || momentum_base != nullptr, "momentum buffer required");
+  r->sgd = enabled != 0;
+  r->grad_base = grad_base; r->param_base = param_base; r->shadow_base = shadow_base; r->momentum_base = momentum_base;
+  r->lr = lr; r->mom = momentum; r->damp = dampening; r->wd = weight_decay; r->nesterov = nesterov;
+  return 0;
 }

@@ -21,7 +21,7 @@ extern "C" {
 #endif
 
 #define B200_MAX_RANKS 8
-#define B200_MAX_COMM_BLOCKS 64
+#define B200_MAX_COMM_BLOCKS 160
 #define B200_SIGNAL_BYTES (1u << 20) /* first MiB of every symmetric arena: signal pads + epochs */
 
 #define B200_DTYPE_F32 0
@@ -73,6 +73,18 @@ int b200_comm_alloc_errflag(int** host_ptr_out, int** dev_ptr_out);
 #define B200_ALGO_NVLS 3
 int b200_allreduce(const b200_comm* comm, size_t offset, size_t count, int dtype, float scale,
                    int algo, int max_blocks, void* stream);
+/* The one algorithm selector (used by B200_ALGO_AUTO, by the reducer and by the Python layer): one-shot up to
+ * oneshot_max_bytes (0 = max(64 KiB, 2 MiB / (world - 1))), then NVLS if a multicast mapping is bound, world > 2 and
+ * bytes >= nvls_min_bytes, else two-shot. */
+int b200_pick_algo(int world, int has_multicast, size_t bytes, size_t oneshot_max_bytes, size_t nvls_min_bytes);
+/* Fused bucket step (the reference's `loss.backward()` all-reduce + `optimizer.step()`, …smddp-gpu.py:167-168, and SMDDP's
+ * "balanced fusion buffer", static/images/training/training24.png): rank r reduces shard r of the bucket's fp32 gradients
+ * (NVLS ld_reduce or P2P loads), applies SGD with momentum to shard r of the fp32 master weights, writes the new weights
+ * (and their bf16 shadow when shadow_offset != 0) into every rank's arena (multimem.st or P2P stores) and zeroes the local
+ * gradients -- one kernel.  All offsets are bytes inside the symmetric arena; `momentum_buf` is local (NULL if momentum == 0). */
+int b200_allreduce_sgd(const b200_comm* comm, size_t grad_offset, size_t param_offset, size_t shadow_offset,
+                       float* momentum_buf, size_t count, float scale, float lr, float momentum, float dampening,
+                       float weight_decay, int nesterov, int algo, int max_blocks, void* stream);
 /* One-shot all-reduce from the symmetric arena into an arbitrary local buffer (out-of-place). */
 int b200_allreduce_oneshot_out(const b200_comm* comm, size_t offset, void* out, size_t count, int dtype,
                                float scale, int max_blocks, void* stream);
@@ -94,6 +106,10 @@ int b200_reducer_was_ready(const b200_reducer* r, int param);
 int b200_reducer_mark_ready(b200_reducer* r, int param, void* producer_stream, void* other_stream, void* comm_stream);
 int b200_reducer_finalize(b200_reducer* r, void* main_stream, void* other_stream, void* comm_stream, int sync_grads);
 int b200_reducer_bucket_algo(const b200_reducer* r, int bucket);
+/* enabled != 0: every bucket launch becomes b200_allreduce_sgd (see there); base offsets are those of element 0 of the flat
+ * gradient / parameter / shadow arenas, momentum_base the local momentum buffer laid out like the parameters */
+int b200_reducer_set_sgd(b200_reducer* r, int enabled, size_t grad_base, size_t param_base, size_t shadow_base,
+                         float* momentum_base, float lr, float momentum, float dampening, float weight_decay, int nesterov);
 
 /* ---------------------------------------------------------------------------------------------
  * Optimizers over flat arenas (replace ATen foreach SGD / Adam — …native-cpu.py:144,156;

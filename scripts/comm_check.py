@@ -42,6 +42,8 @@ def main():
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--out", type=str, default="")
     ap.add_argument("--graph", action="store_true", help="time the all-reduces inside one CUDA graph (no host launch cost)")
+    ap.add_argument("--ctas", type=str, default="", help="comma list of CTA counts: also time NVLS / two-shot with each (>= 1 MiB)")
+    ap.add_argument("--skip-correct", action="store_true")
     a = ap.parse_args()
     bd.init_process_group(backend="b200")
     rank, world = bd.get_rank(), bd.get_world_size()
@@ -53,7 +55,7 @@ def main():
     arena_f32, off = comm.alloc_arena(max(a.max_mb << 20, big) // 4, torch.float32)
     ok_all = True
     # ------------------------------------------------------------------ correctness
-    for dtype in (torch.float32, torch.bfloat16):
+    for dtype in (() if a.skip_correct else (torch.float32, torch.bfloat16)):
         es = 4 if dtype == torch.float32 else 2
         view = arena_f32.view(torch.uint8).view(dtype)
         for nbytes in (16, 1024, 4096 + 16, 248 * 1024 + 32, 2052000 // 16 * 16, 8 << 20, 15853824, 28852224):
@@ -102,10 +104,17 @@ def main():
     if a.sweep:
         nccl_group = dist.new_group(backend="nccl") if a.nccl else None
         sizes = [1 << s for s in range(10, 31) if (1 << s) <= (a.max_mb << 20)]
+        cta_list = [int(c) for c in a.ctas.split(",") if c]
+        base_ctas = comm.cfg.max_ctas
         for nbytes in sizes:
             n = nbytes // 4
             row = {"bytes": nbytes}
-            for algo in algos:
+            variants = [(algo, base_ctas, L.ALGO_NAMES[algo]) for algo in algos]
+            if nbytes >= (1 << 20):
+                big_algo = L.ALGO_NVLS if comm.has_nvls else L.ALGO_TWOSHOT
+                variants += [(big_algo, c, "%s_c%d" % (L.ALGO_NAMES[big_algo], c)) for c in cta_list]
+            for algo, ctas, label in variants:
+                comm.cfg.max_ctas = ctas
                 if algo == L.ALGO_ONESHOT and nbytes > (8 << 20):
                     continue
                 for _ in range(3):
@@ -131,8 +140,9 @@ def main():
                     e.record()
                 torch.cuda.synchronize()
                 us = bd.max_over_ranks(s.elapsed_time(e) / a.iters * 1e3)
-                row[L.ALGO_NAMES[algo] + "_us"] = us
-                row[L.ALGO_NAMES[algo] + "_busbw_GBs"] = nbytes / (us * 1e-6) * 2 * (world - 1) / world / 1e9
+                row[label + "_us"] = us
+                row[label + "_busbw_GBs"] = nbytes / (us * 1e-6) * 2 * (world - 1) / world / 1e9
+            comm.cfg.max_ctas = base_ctas
             if nccl_group is not None:
                 x = torch.ones(n, device=dev)
                 for _ in range(3):
