@@ -10,6 +10,13 @@ meta-evaluation (the reference does that; it keeps dropout active).
 Changed: the reference re-reads one checkpoint file from disk per step (``torch.load(x)``, :49) — here a
 ``ShadowBank`` loads every checkpoint once (``weights_only=True``: they come from an untrusted tree) and keeps
 the state dicts on the training device; ``np.asscalar`` (removed from numpy) is replaced.
+
+The epoch loops are built for a GPU, where this workload is pure latency (a 10-image batch through a small CNN):
+the shadow model is never ``load_state_dict``-ed (14 device copies per step) -- it is evaluated *functionally* on the
+bank's tensors (``torch.nn.utils.stateless``), and nothing is read back per step: losses and scores stay on the device
+and cross to the host once per epoch (the reference's two ``.item()`` calls per model are two full pipeline drains).
+On CUDA the meta-classifier's own MLP and loss run on this package's kernels (strided fp32 GEMM of ``csrc/seq.cu``,
+fused BCE-with-logits of ``csrc/loss.cu``) instead of cuBLAS / ATen.
 """
 from __future__ import annotations
 
@@ -19,8 +26,17 @@ import numpy as np
 import torch
 import torch.nn as nn
 import torch.nn.functional as F
+from torch.nn.utils import stateless
 
 from ...models.mntd.models import MODELS
+from ...ops import functional as BF
+
+
+def _linear(x, layer: nn.Linear):
+    """``layer(x)``: on CUDA the fp32 GEMM of this package, on the CPU torch's."""
+    if x.is_cuda:
+        return BF.linear_f32(x.reshape(1, -1).float(), layer.weight, layer.bias).reshape(-1)
+    return layer(x)
 
 
 def load_model_setting(task: str):
@@ -49,11 +65,13 @@ class MetaClassifier(nn.Module):
             self.cuda()
 
     def forward(self, pred):
-        emb = F.relu(self.fc(pred.reshape(self.N_in * self.class_num).to(self.fc.weight.dtype)))
-        return self.output(emb)
+        emb = F.relu(_linear(pred.reshape(self.N_in * self.class_num).to(self.fc.weight.dtype), self.fc))
+        return _linear(emb, self.output)
 
     def loss(self, score, y):
-        y_var = torch.tensor([float(y)], device=score.device)
+        y_var = y if torch.is_tensor(y) else torch.tensor([float(y)], device=score.device)
+        if score.is_cuda:
+            return BF.bce_with_logits(score.reshape(1), y_var.reshape(1).to(score.device))
         return F.binary_cross_entropy_with_logits(score, y_var)
 
 
@@ -73,7 +91,7 @@ class MetaClassifierOC(nn.Module):
             self.cuda()
 
     def forward(self, pred, ret_feature=False):
-        emb = F.relu(self.fc(pred.reshape(self.N_in * self.class_num).to(self.fc.weight.dtype)))
+        emb = F.relu(_linear(pred.reshape(self.N_in * self.class_num).to(self.fc.weight.dtype), self.fc))
         return emb if ret_feature else torch.dot(emb, self.w)
 
     def loss(self, score):
@@ -102,10 +120,29 @@ class ShadowBank:
         model.load_state_dict(self.states[path] if path in self.states else
                               torch.load(path, map_location=self.device, weights_only=True))
 
+    def state(self, path: str) -> Dict[str, torch.Tensor]:
+        if path not in self.states:
+            sd = torch.load(path, map_location="cpu", weights_only=True)
+            self.states[path] = {(k[7:] if k.startswith("module.") else k): v.to(self.device) for k, v in sd.items()}
+        return self.states[path]
 
-def _score(meta_model, basic_model, is_discrete):
-    out = basic_model.emb_forward(meta_model.inp) if is_discrete else basic_model.forward(meta_model.inp)
+
+def _score(meta_model, basic_model, is_discrete, state=None):
+    """Trojan score of one shadow model.  ``state``: evaluate ``basic_model``'s architecture on these tensors without
+    copying them into the module (the checkpoint stays where the bank put it)."""
+    if state is None:
+        out = basic_model.emb_forward(meta_model.inp) if is_discrete else basic_model.forward(meta_model.inp)
+    else:
+        with stateless._reparametrize_module(basic_model, state):
+            out = basic_model.emb_forward(meta_model.inp) if is_discrete else basic_model.forward(meta_model.inp)
     return meta_model.forward(out)
+
+
+def _to_host(tensors) -> np.ndarray:
+    """One device->host transfer for a whole epoch's worth of scalars."""
+    if not tensors:
+        return np.zeros(0, dtype=np.float64)
+    return torch.stack([t.detach().reshape(()).float() for t in tensors]).cpu().double().numpy()
 
 
 def _auc_acc(preds, labs, threshold):
@@ -122,36 +159,40 @@ def epoch_meta_train(meta_model, basic_model, optimizer, dataset: List[Tuple[str
     meta_model.train()
     basic_model.train()
     bank = bank or ShadowBank([x for x, _ in dataset], next(meta_model.parameters()).device)
-    cum_loss, preds, labs = 0.0, [], []
+    dev = next(meta_model.parameters()).device
+    targets = {0: torch.zeros(1, device=dev), 1: torch.ones(1, device=dev)}
+    losses, scores, labs = [], [], []
     for i in np.random.permutation(len(dataset)):
         x, y = dataset[i]
-        bank.load_into(basic_model, x)
-        score = _score(meta_model, basic_model, is_discrete)
-        l = meta_model.loss(score, y)
+        score = _score(meta_model, basic_model, is_discrete, bank.state(x))
+        l = meta_model.loss(score, targets[int(y)])
         optimizer.zero_grad()
         l.backward()
         optimizer.step()
-        cum_loss += float(l.item())
-        preds.append(float(score.item()))
+        losses.append(l)                      # stays on the device: no per-model host synchronisation
+        scores.append(score)
         labs.append(y)
+    preds = _to_host(scores)
     auc, acc = _auc_acc(preds, labs, threshold)
-    return cum_loss / len(dataset), auc, acc
+    return float(_to_host(losses).sum()) / len(dataset), auc, acc
 
 
 def epoch_meta_eval(meta_model, basic_model, dataset, is_discrete, threshold=0.0, bank: ShadowBank = None):
     meta_model.eval()
     basic_model.train()                      # as in the reference (utils_meta.py:76)
     bank = bank or ShadowBank([x for x, _ in dataset], next(meta_model.parameters()).device)
-    cum_loss, preds, labs = 0.0, [], []
+    dev = next(meta_model.parameters()).device
+    targets = {0: torch.zeros(1, device=dev), 1: torch.ones(1, device=dev)}
+    losses, scores, labs = [], [], []
     with torch.no_grad():
         for x, y in dataset:
-            bank.load_into(basic_model, x)
-            score = _score(meta_model, basic_model, is_discrete)
-            cum_loss += float(meta_model.loss(score, y).item())
-            preds.append(float(score.item()))
+            score = _score(meta_model, basic_model, is_discrete, bank.state(x))
+            losses.append(meta_model.loss(score, targets[int(y)]))
+            scores.append(score)
             labs.append(y)
+    preds = _to_host(scores)
     auc, acc = _auc_acc(preds, labs, threshold)
-    return cum_loss / len(preds), auc, acc
+    return float(_to_host(losses).sum()) / max(len(preds), 1), auc, acc
 
 
 def epoch_meta_train_oc(meta_model, basic_model, optimizer, dataset, is_discrete, bank: ShadowBank = None):
@@ -177,7 +218,6 @@ def epoch_meta_eval_oc(meta_model, basic_model, dataset, is_discrete, threshold=
     preds, labs = [], []
     with torch.no_grad():
         for x, y in dataset:
-            bank.load_into(basic_model, x)
-            preds.append(float(_score(meta_model, basic_model, is_discrete).item()))
+            preds.append(_score(meta_model, basic_model, is_discrete, bank.state(x)))
             labs.append(y)
-    return _auc_acc(preds, labs, threshold)
+    return _auc_acc(_to_host(preds), labs, threshold)

@@ -120,8 +120,8 @@ static int reducer_launch(b200_reducer* r, int b, cudaStream_t producer, cudaStr
     // CTA budget: the fused step also streams the optimizer's traffic (p, m read/write of the owned shard, zeroing of the
     // bucket's gradients), so it gets more CTAs than a bare all-reduce; the LAST bucket completes with the last wgrad
     // kernel of backward, nothing is left to overlap with and it is on the critical path: it takes most of the machine.
-    static const int fused_ctas = []() { const char* e = getenv("B200DDP_FUSED_CTAS"); return e ? atoi(e) : 32; }();
-    static const int tail_ctas = []() { const char* e = getenv("B200DDP_FUSED_TAIL_CTAS"); return e ? atoi(e) : 128; }();
+    static const int fused_ctas = []() { const char* e = getenv("B200DDP_FUSED_CTAS"); return e ? atoi(e) : 16; }();
+    static const int tail_ctas = []() { const char* e = getenv("B200DDP_FUSED_TAIL_CTAS"); return e ? atoi(e) : 64; }();
     const bool last = b + 1 == (int)r->count.size();
     const int blocks = std::max(r->max_blocks, last ? tail_ctas : fused_ctas);
     return b200_allreduce_sgd(&r->comm, r->offset[b], r->param_base + elem0 * sizeof(float),
@@ -130,8 +130,8 @@ static int reducer_launch(b200_reducer* r, int b, cudaStream_t producer, cudaStr
   }
   const int algo = reducer_pick_algo(r, bytes);
   r->algo_used[b] = algo;
-  // the last bucket has nothing left to overlap with: B200DDP_TAIL_CTAS (default 64; measured 1.098 -> 1.045 ms per resnet18 step on 2 GPUs)
-  static const int tail_ctas = []() { const char* e = getenv("B200DDP_TAIL_CTAS"); return e ? atoi(e) : 64; }();
+  // the last bucket has nothing left to overlap with: B200DDP_TAIL_CTAS (default 32: resnet18 step on 2 GPUs 1.098 -> 1.049 ms; on 8 GPUs it makes no difference)
+  static const int tail_ctas = []() { const char* e = getenv("B200DDP_TAIL_CTAS"); return e ? atoi(e) : 32; }();
   if (tail_ctas > 0 && b + 1 == (int)r->count.size())
     return b200_allreduce(&r->comm, r->offset[b], r->count[b], r->dtype, r->scale, algo, std::max(r->max_blocks, tail_ctas), comm);
   return b200_allreduce(&r->comm, r->offset[b], r->count[b], r->dtype, r->scale, algo, r->max_blocks, comm);

@@ -215,3 +215,26 @@ def test_speech_command_loader_reads_the_reference_npy_layout(tmp_path):
     assert UB.SPEECH_USED_CLS[ds[0][1]] == UB.SPEECH_ALL_CLS[labels[keep[0]]] and ds[0][0].shape == (16000,)
     _, _, trainset, testset, is_binary, _, _, _, _ = UB.load_dataset_setting("audio", root=str(tmp_path))
     assert isinstance(trainset, UB.SpeechCommand) and isinstance(testset, UB.SpeechCommand) and not is_binary
+
+
+@pytest.mark.parametrize("mode", ["ddp", "replica"])
+def test_zoo_trainer_distributed_modes_world2(tmp_path, mode):
+    """The intent of the reference's two unparsable attempts (``train_basic_{jumbo,trojaned}_distributed_cpu.py``:
+    ``DistributedSampler`` + ``DDP(model)`` + rank-0 save, :55-68) on gloo at world 2: ``--mode ddp`` data-parallelises every
+    model, ``--mode replica`` deals the model indices out over the ranks.  Both must write every checkpoint exactly once,
+    un-prefixed, loadable into the model definition, plus the JSON log."""
+    from b200ddp.models.mntd.models import MODELS
+    from b200ddp.utils.launch import launch
+    root = str(tmp_path / "ckpt")
+    rc = launch(2, ["jumbo", "--task", "mnist", "--save", root, "--num", "4", "--epochs", "1", "--synthetic-size", "256",
+                    "--mode", mode, "--seed", "5"], module="b200ddp.workloads.mntd.train_basic", timeout=600)
+    assert rc == 0
+    names = sorted(os.listdir(os.path.join(root, "mnist", "models")))
+    assert names == ["shadow_jumbo_%d.model" % i for i in range(4)]
+    for n in names:
+        sd = torch.load(os.path.join(root, "mnist", "models", n), map_location="cpu", weights_only=True)
+        assert not any(k.startswith("module.") for k in sd)
+        MODELS["mnist"](gpu=False).load_state_dict(sd)
+    import json
+    log = json.load(open(os.path.join(root, "mnist", "jumbo.log")))
+    assert log["models"] == (4 if mode == "replica" else 4) and 0.0 <= log["acc"] <= 1.0
