@@ -130,6 +130,10 @@ def run_own(args) -> dict:
         dev_ms, e2e_ms, last = _time_steps(bd, torch, step, xs, ys, args.warmup, args.steps, flush, dev)
         if ddp_check is not None:
             ddp_check["params_identical_after_bench"] = params_identical(model)
+        try:        # where an (eager) step spends its time: forward / backward / exposed collective tail / optimizer
+            phase_ms = step.breakdown(xs[0], ys[0], iters=5)
+        except Exception as e:
+            phase_ms = {"error": "%s: %s" % (type(e).__name__, str(e)[:160])}
         comm = bd.get_comm()
         if comm is not None:
             comm.check_health()
@@ -195,7 +199,8 @@ def run_own(args) -> dict:
                    "per_gpu_batch": per_rank, "optimizer": "SGD lr=0.01 momentum=0.9", "cuda_graph": step._graph is not None,
                    "l2": "256 MiB buffer written between timed iterations (outside the event pair)",
                    "launches_per_step": launches_per_step, "allreduce_algos": algos, "final_loss": last,
-                   "ddp_check": ddp_check, "secondary": secondary, "like_for_like": lfl,
+                   "ddp_check": ddp_check, "phase_ms_eager": phase_ms, "fused_optimizer": bool(getattr(step, "fused_optimizer", False)),
+                   "secondary": secondary, "like_for_like": lfl,
                    "baseline_note": "the reference publishes no number (BASELINE.md); vs_baseline is null"},
     }
     bd.destroy_process_group()

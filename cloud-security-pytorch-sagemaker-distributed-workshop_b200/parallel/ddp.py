@@ -217,7 +217,13 @@ class DistributedDataParallel(nn.Module):
         if self.device.type == "cuda":
             from ..ops import streams
             streams.join(self.device)      # wgrad kernels forked onto the aux stream
+        ev = getattr(self, "_phase_events", None)
+        if ev is not None:                 # TrainStep.breakdown(): where the compute of backward ends and the join begins
+            ev["bwd_compute_end"].record()
         self.reducer.finalize()
+        if ev is not None:
+            ev["comm_joined"].record()
+            ev["hit"] = True
         if self.require_backward_grad_sync:
             self._accum_count = 0
         else:

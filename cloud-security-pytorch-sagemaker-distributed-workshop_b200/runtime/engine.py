@@ -275,6 +275,56 @@ class TrainStep:
             self._pipe["views"] = [self._views(b) for b in self._pipe["stage"]]
             self._pipe["pin_off_np"] = [t.numpy() for t in self._pipe["pin_off"]]
 
+    def breakdown(self, x_u8: torch.Tensor, y: torch.Tensor, iters: int = 5) -> dict:
+        """Device-timed phases of one EAGER step (CUDA events on the step's stream, mean over ``iters``, max over ranks):
+        ``forward`` (augmentation + model + loss), ``backward`` (until the last gradient kernel of this rank has been
+        queued behind), ``exposed_comm`` (what the step still waits for once backward's compute is done: the tail of the
+        bucket collectives -- with the fused bucket step that includes the optimizer of the last bucket), ``optimizer``
+        (the separate optimizer pass; ~0 when it is fused into the collectives).  These are real optimizer steps.  Eager
+        launches pay host latency the captured graph does not, so the sum is larger than ``ms_per_step`` of a replay;
+        the split is what it is for."""
+        if not self.cuda:
+            return {}
+        from ..ops import native as nv
+        from ..parallel import process_group as pg
+        dev = self.device
+        xd, yd = x_u8.to(dev), y.to(dev)
+        off = self._draw_offsets(xd.shape[0]).to(dev) if self.augment else None
+        ddp = self.model if hasattr(self.model, "_finalize_backward") else None
+        tot = dict.fromkeys(("forward", "backward", "exposed_comm", "optimizer"), 0.0)
+        for it in range(iters + 1):
+            ev = {k: torch.cuda.Event(enable_timing=True) for k in ("t0", "t1", "bwd_compute_end", "comm_joined", "t2", "t3")}
+            if ddp is not None:
+                ddp._phase_events = ev
+            torch.cuda.synchronize(dev)
+            ev["t0"].record()
+            if self._net_mega is not None:
+                self.optimizer.zero_grad()
+                loss = self._net_mega.fused_loss(xd, yd, aug=(off, self.mean_t, self.inv_std_t))
+            else:
+                inp = nv.augment(xd, off, self.mean_t, self.inv_std_t, c_out=8)
+                self.optimizer.zero_grad()
+                loss = self.criterion(self.model(inp), yd)
+            ev["t1"].record()
+            loss.backward(self._one)
+            ev["t2"].record()
+            self.optimizer.step()
+            ev["t3"].record()
+            torch.cuda.synchronize(dev)
+            if ddp is not None:
+                ddp._phase_events = None
+            self.steps_done += 1
+            if it == 0:
+                continue                     # first pass: lazy allocations
+            tot["forward"] += ev["t0"].elapsed_time(ev["t1"])
+            if ev.get("hit"):
+                tot["backward"] += ev["t1"].elapsed_time(ev["bwd_compute_end"])
+                tot["exposed_comm"] += ev["bwd_compute_end"].elapsed_time(ev["comm_joined"])
+            else:
+                tot["backward"] += ev["t1"].elapsed_time(ev["t2"])
+            tot["optimizer"] += ev["t2"].elapsed_time(ev["t3"])
+        return {k: pg.max_over_ranks(v / iters) for k, v in tot.items()}
+
     def flush_counters(self):
         if self.cuda:
             bmod.flush_bn_counters(self.model, self.steps_done - getattr(self, "_flushed", 0))

@@ -21,8 +21,28 @@ def _act(n, c, h, w, dev, scale=1.0):
     return x
 
 
+@pytest.fixture(autouse=True)
+def _strict_fp32_oracle():
+    """The oracles below are torch ops on fp32 GPU tensors: keep cuDNN / cuBLAS from evaluating THEM in TF32."""
+    saved = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = saved
+
+
+BF16_EPS = 2.0 ** -8
+
+
 def _rel_err(a, b):
+    """Relative Frobenius error; also ASSERTS an elementwise bound (a few bf16 ulps of the largest reference value), so a
+    wrong border row or one bad tile tail of a many-tile problem cannot hide inside the norm."""
     a, b = a.float(), b.float()
+    if a.shape == b.shape and b.numel() > 0:
+        max_abs = float((a - b).abs().max())
+        scale = float(b.abs().max())
+        assert max_abs <= 6.0 * BF16_EPS * scale + 1e-6, "elementwise error %.3e exceeds %.3e (largest reference value %.3e)" % (
+            max_abs, 6.0 * BF16_EPS * scale, scale)
     return float((a - b).norm() / (b.norm() + 1e-12))
 
 
