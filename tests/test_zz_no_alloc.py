@@ -77,4 +77,14 @@ def test_bn_stats_noalloc_rejects_oversized_problem():
     assert rc != 0
     msg = lib.b200_last_error().decode()
     assert "needs" in msg and "built-in array" in msg
+    # the documented boundary: 1 MiB = 4 KiB of counters + 2040 tiles of 512 B.  C = 1024 is 16 channel groups, so 127 row blocks
+    # (rows < 32768) fit and 128 do not; C = 960 (15 groups) fits at any row count
+    limit = 1 << 20
+    assert lib.b200_bn_scratch_bytes(c_size_t(32767), c_int(1024)) <= limit
+    assert lib.b200_bn_scratch_bytes(c_size_t(32768), c_int(1024)) > limit
+    assert lib.b200_bn_scratch_bytes(c_size_t(1 << 24), c_int(960)) <= limit
+    g1 = torch.ones(1024, device=dev)
+    stat1 = torch.zeros(4, 1024, device=dev)
+    rc = lib.b200_bn_stats_noalloc(*_args(x, 32768, 1024, g1, g1, stat1, g1, g1), c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc != 0 and "built-in array" in lib.b200_last_error().decode()
     torch.cuda.synchronize()
