@@ -166,7 +166,8 @@ def run_own(args) -> dict:
                 import torch_tuned
                 offs = torch.stack([torch.randint(0, 9, (nb, per_rank), generator=g), torch.randint(0, 9, (nb, per_rank), generator=g),
                                     torch.randint(0, 2, (nb, per_rank), generator=g)], -1).to(torch.int32).pin_memory()
-                lfl = torch_tuned.run_all(args.model, per_rank, hw, args.steps, args.warmup, xs, ys, offs, world, dev)
+                lfl = torch_tuned.run_all(args.model, per_rank, hw, args.steps, args.warmup, xs, ys, offs, world, dev,
+                                          modes=tuple(m for m in args.lfl_modes.split(",") if m))
             except Exception as e:
                 lfl = {"error": "%s: %s" % (type(e).__name__, str(e)[:200])}
     imgs = args.steps * per_rank * world
@@ -219,6 +220,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-like-for-like", action="store_true")
     ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--lfl-modes", type=str, default="fp32,fp32_graph,bf16_graph", help="stock-PyTorch modes to measure alongside")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl in ("reference", "reference_on_b200", "torch_tuned"):
