@@ -19,6 +19,38 @@ from ..ops import functional as BF
 _FUSE_BN_STATS = [__import__("os").environ.get("B200DDP_FUSE_BN_STATS", "1") != "0"]
 
 
+# Pooled BN statistics (set up by runtime.engine.TrainStep, active only inside its step body).  A conv whose epilogue produces
+# the statistics of the following BatchNorm accumulates them in a small fp32 buffer that has to be zero again before the next
+# forward.  Stand-alone, a tiny finalize kernel per layer reads and clears it.  A step engine knows where a step begins: while
+# it is active every layer's buffer is a slice of ONE pool that is cleared by ONE memset per step, and BatchNorm derives
+# scale / shift from the sums inside its apply kernel (`b200_bn_apply_sums_keep`): one launch per BN layer less.
+_POOL_ACTIVE = [False]
+_POOLS = {}
+_POOL_FLOATS = 1 << 18
+
+
+def _pool_alloc(device, n: int) -> torch.Tensor:
+    key = (device.type, device.index)
+    pool = _POOLS.get(key)
+    if pool is None:
+        pool = {"buf": torch.zeros(_POOL_FLOATS, dtype=torch.float32, device=device), "used": 0}
+        _POOLS[key] = pool
+    n = (n + 63) // 64 * 64
+    if pool["used"] + n > _POOL_FLOATS:
+        return None
+    t = pool["buf"][pool["used"]: pool["used"] + n]
+    pool["used"] += n
+    t._b200_pooled = True
+    return t
+
+
+def zero_bn_sum_pool(device) -> None:
+    """One memset over every pooled BN-statistics buffer of ``device`` (start of a step)."""
+    pool = _POOLS.get((device.type, device.index))
+    if pool is not None and pool["used"]:
+        pool["buf"][: pool["used"]].zero_()
+
+
 class Conv2d(nn.Conv2d):
     """conv (+bias) with an optional fused ReLU epilogue."""
 
@@ -31,6 +63,7 @@ class Conv2d(nn.Conv2d):
         # registered as a child module (state_dict keys stay torch's) while deepcopy / pickle still carry the pairing along.
         object.__setattr__(self, "_bn_pair", None)
         self._bn_sums = None
+        self._bn_sums_pooled = None
 
     def fuse_bn_stats(self, bn: "BatchNorm2d"):
         """Declare that ``bn`` normalises exactly this conv's output.  In training mode on CUDA the conv epilogue then
@@ -52,10 +85,17 @@ class Conv2d(nn.Conv2d):
             rows = n * ho * wo
             if rows > BF.nv.BN_SMALL_ROWS:      # small tensors: BN's single-launch kernel is cheaper than finalize + apply
                 kp = BF.ceil8(self.out_channels)
-                if self._bn_sums is None or self._bn_sums.device != x.device:
-                    self._bn_sums = torch.zeros(2 * kp + 1, dtype=torch.float32, device=x.device)   # sums + ticket, zero at rest
-                y = BF.conv2d(x, self.weight, None, self.stride[0], self.padding[0], False, self._bn_sums)
-                y._b200_bn_sums = self._bn_sums
+                sums = None
+                if _POOL_ACTIVE[0]:
+                    if self._bn_sums_pooled is None or self._bn_sums_pooled.device != x.device:
+                        self._bn_sums_pooled = _pool_alloc(x.device, 2 * kp + 1)
+                    sums = self._bn_sums_pooled
+                if sums is None:
+                    if self._bn_sums is None or self._bn_sums.device != x.device:
+                        self._bn_sums = torch.zeros(2 * kp + 1, dtype=torch.float32, device=x.device)   # sums + ticket, zero at rest
+                    sums = self._bn_sums
+                y = BF.conv2d(x, self.weight, None, self.stride[0], self.padding[0], False, sums)
+                y._b200_bn_sums = sums
                 return y
         return BF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0], self.fused_relu)
 

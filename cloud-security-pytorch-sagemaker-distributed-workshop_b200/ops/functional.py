@@ -321,8 +321,14 @@ class _BatchNormFn(torch.autograd.Function):
             # the producing conv already accumulated sum / sum of squares per channel in its epilogue
             # (nv.bn_apply_sums does both in one launch, but its per-CTA ticket -- fence + same-address atomic -- measured
             # 10% slower per resnet18 step than the tiny finalize kernel, whose launch hides behind the conv's tail)
-            stat = nv.bn_finalize(presummed, rows, gamma.detach(), beta.detach(), eps, momentum, running_mean, running_var)
-            y = nv.bn_apply(x, residual, stat, relu)
+            if getattr(presummed, "_b200_pooled", False):
+                # a step engine clears every layer's sums with one memset per step: scale / shift are derived inside the
+                # apply kernel, no finalize launch (nn/modules.py)
+                y, stat = nv.bn_apply_sums(x, residual, presummed, gamma.detach(), beta.detach(), eps, momentum, running_mean,
+                                           running_var, relu, keep=True)
+            else:
+                stat = nv.bn_finalize(presummed, rows, gamma.detach(), beta.detach(), eps, momentum, running_mean, running_var)
+                y = nv.bn_apply(x, residual, stat, relu)
         elif training and rows <= nv.BN_SMALL_ROWS:
             y, stat = nv.bn_fwd_fused(x, residual, gamma.detach(), beta.detach(), eps, momentum, running_mean, running_var, relu)
         else:

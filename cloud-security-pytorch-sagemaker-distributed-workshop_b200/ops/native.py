@@ -204,13 +204,15 @@ def bn_finalize(sums: torch.Tensor, rows: int, gamma, beta, eps: float, momentum
     return stat
 
 
-def bn_apply_sums(x, residual, sums, gamma, beta, eps: float, momentum: float, running_mean, running_var, relu: bool):
-    """``bn_finalize`` + ``bn_apply`` in one launch; ``sums`` holds 2C floats + 1 ticket word.  Returns (y, stat)."""
+def bn_apply_sums(x, residual, sums, gamma, beta, eps: float, momentum: float, running_mean, running_var, relu: bool,
+                  keep: bool = False):
+    """``bn_finalize`` + ``bn_apply`` in one launch; ``sums`` holds 2C floats + 1 ticket word.  ``keep``: leave ``sums`` as
+    they are (no ticket; the caller clears them before the next forward).  Returns (y, stat)."""
     rows, C = _rows_c(x)
     assert sums.numel() >= 2 * C + 1
     stat = torch.empty((4, C), dtype=torch.float32, device=x.device)
     y = torch.empty_like(x)
-    L.check(_fn("b200_bn_apply_sums", x)(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(sums), L.ptr(gamma),
+    L.check(_fn("b200_bn_apply_sums_keep" if keep else "b200_bn_apply_sums", x)(L.ptr(x), L.ptr(residual), L.ptr(y), c_size_t(rows), c_int(C), L.ptr(sums), L.ptr(gamma),
                                        L.ptr(beta), c_float(eps), c_float(momentum), L.ptr(stat), L.ptr(running_mean),
                                        L.ptr(running_var), c_int(int(relu)), L.stream_ptr()), "bn_apply_sums")
     return y, stat

@@ -64,6 +64,7 @@ class TrainStep:
             self._comm = _pg.get_comm()         # polled after every step: a timed-out collective must not go unnoticed
             BF.assume_unit_loss_grad(True)
             bmod.defer_bn_counters(True)
+            self._pool_bn = os.environ.get("B200DDP_POOL_BN_SUMS", "1") not in ("0", "false", "off")
             # this engine owns the whole step, so the optimizer may move into the gradient collective (world > 1)
             fuse = getattr(optimizer, "fuse_into_backward", None)
             self.fused_optimizer = bool(fuse(True)) if fuse is not None else False
@@ -103,7 +104,16 @@ class TrainStep:
         else:
             inp = augment_reference(x_u8, train_transform=self.augment, mean=self._mean, std=self._std, offsets=offsets)
         self.optimizer.zero_grad()
-        out = self.model(inp)
+        if self.cuda and self._pool_bn:
+            # this engine knows where a step starts: all conv-epilogue BN statistics live in one pool, cleared here once
+            bmod.zero_bn_sum_pool(self.device)
+            bmod._POOL_ACTIVE[0] = True
+            try:
+                out = self.model(inp)
+            finally:
+                bmod._POOL_ACTIVE[0] = False
+        else:
+            out = self.model(inp)
         loss = self.criterion(out, y)
         loss.backward(self._one if self.cuda else None)
         self.optimizer.step()

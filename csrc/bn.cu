@@ -235,7 +235,8 @@ __global__ void __launch_bounds__(kThreads)
 bn_apply_sums_kernel(const T* __restrict__ x, const T* __restrict__ res,
                      T* __restrict__ y, size_t rows, int C, float* __restrict__ sums,
                      const float* __restrict__ gamma, const float* __restrict__ beta, float eps, float momentum,
-                     float* __restrict__ stat, float* __restrict__ running_mean, float* __restrict__ running_var) {
+                     float* __restrict__ stat, float* __restrict__ running_mean, float* __restrict__ running_var,
+                     int keep_sums) {
   pdl_trigger();
   pdl_wait();
   __shared__ bool last;
@@ -266,17 +267,19 @@ bn_apply_sums_kernel(const T* __restrict__ x, const T* __restrict__ res,
       }
     }
   }
-  __syncthreads();                                            // every thread of this CTA has read its sums
-  if (threadIdx.x == 0) {
-    unsigned* counter = reinterpret_cast<unsigned*>(sums + 2 * C);
-    __threadfence();
-    const unsigned ticket = atomicAdd(counter, 1u);
-    last = ticket == gridDim.x * gridDim.y - 1;
-    if (last) *counter = 0u;
-  }
-  __syncthreads();
-  if (last) {
-    for (int i = threadIdx.x; i < 2 * C; i += kThreads) sums[i] = 0.f;
+  if (!keep_sums) {                                           // keep_sums: the caller clears all its sum buffers at once later
+    __syncthreads();                                          // every thread of this CTA has read its sums
+    if (threadIdx.x == 0) {
+      unsigned* counter = reinterpret_cast<unsigned*>(sums + 2 * C);
+      __threadfence();
+      const unsigned ticket = atomicAdd(counter, 1u);
+      last = ticket == gridDim.x * gridDim.y - 1;
+      if (last) *counter = 0u;
+    }
+    __syncthreads();
+    if (last) {
+      for (int i = threadIdx.x; i < 2 * C; i += kThreads) sums[i] = 0.f;
+    }
   }
   if (!live) return;
   for (size_t r = (size_t)blockIdx.x * kRL + rl; r < rows; r += (size_t)gridDim.x * kRL) {
@@ -990,14 +993,14 @@ extern "C" int b200_bn_finalize(float* sums, size_t rows, int C, const float* ga
 template <typename T>
 static int b200_bn_apply_sums_impl(const void* xv, const void* resv, void* yv, size_t rows, int C, float* sums, const float* gamma,
                                    const float* beta, float eps, float momentum, float* stat, float* running_mean,
-                                   float* running_var, int relu, void* stream) {
+                                   float* running_var, int relu, void* stream, int keep_sums = 0) {
   B200_REQUIRE(xv && yv && sums && gamma && beta && stat, "null argument");
   B200_REQUIRE(C % 8 == 0 && C > 0 && rows > 0, "C must be a positive multiple of 8");
   dim3 g = bn_grid(rows, C, 8);
   cudaStream_t s = (cudaStream_t)stream;
   const T *x = (const T*)xv, *r = (const T*)resv;
   T* y = (T*)yv;
-#define B200_BNAS(R, S) b200_launch(bn_apply_sums_kernel<T, R, S>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, sums, gamma, beta, eps, momentum, stat, running_mean, running_var)
+#define B200_BNAS(R, S) b200_launch(bn_apply_sums_kernel<T, R, S>, dim3(g), dim3(kThreads), 0, s, x, r, y, rows, C, sums, gamma, beta, eps, momentum, stat, running_mean, running_var, keep_sums)
   if (relu && r) B200_BNAS(true, true);
   else if (relu) B200_BNAS(true, false);
   else if (r) B200_BNAS(false, true);
@@ -1010,3 +1013,19 @@ B200_BN_BOTH(b200_bn_apply_sums,
              (const void* x, const void* residual, void* y, size_t rows, int C, float* sums, const float* gamma, const float* beta,
               float eps, float momentum, float* stat, float* running_mean, float* running_var, int relu, void* stream),
              (x, residual, y, rows, C, sums, gamma, beta, eps, momentum, stat, running_mean, running_var, relu, stream))
+
+// The same single launch WITHOUT the ticket and the clearing of `sums`: for callers that clear all their sum buffers in one go
+// before the next forward (runtime/engine.py keeps every layer's sums in one pooled buffer and zeroes it once per step) -- the
+// per-CTA fence + same-address atomic of the ticket is what made b200_bn_apply_sums slower than finalize + apply.
+extern "C" int b200_bn_apply_sums_keep(const void* x, const void* residual, void* y, size_t rows, int C, float* sums,
+                                       const float* gamma, const float* beta, float eps, float momentum, float* stat,
+                                       float* running_mean, float* running_var, int relu, void* stream) {
+  return b200_bn_apply_sums_impl<__nv_bfloat16>(x, residual, y, rows, C, sums, gamma, beta, eps, momentum, stat, running_mean,
+                                                running_var, relu, stream, 1);
+}
+extern "C" int b200_bn_apply_sums_keep_f32(const void* x, const void* residual, void* y, size_t rows, int C, float* sums,
+                                           const float* gamma, const float* beta, float eps, float momentum, float* stat,
+                                           float* running_mean, float* running_var, int relu, void* stream) {
+  return b200_bn_apply_sums_impl<float>(x, residual, y, rows, C, sums, gamma, beta, eps, momentum, stat, running_mean, running_var,
+                                        relu, stream, 1);
+}

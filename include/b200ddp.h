@@ -247,6 +247,11 @@ int b200_bn_finalize(float* sums, size_t rows, int C, const float* gamma, const 
 int b200_bn_apply_sums(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C, float* sums,
                        const float* gamma, const float* beta, float eps, float momentum, float* stat,
                        float* running_mean, float* running_var, int relu, void* stream);
+/* same launch without the ticket and without clearing `sums`: the caller zeroes all its sum buffers at once before the next
+   forward (one pooled buffer, one memset per step) */
+int b200_bn_apply_sums_keep(const void* x_bf16, const void* residual_bf16, void* y_bf16, size_t rows, int C, float* sums,
+                            const float* gamma, const float* beta, float eps, float momentum, float* stat,
+                            float* running_mean, float* running_var, int relu, void* stream);
 int b200_conv_dgrad(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream);
 /* dx = dgrad(dy, w) + residual: the gradient of the other branch of a forked tensor (ResNet skip) added in the epilogue */
 int b200_conv_dgrad_add(const void* dy, const void* w, void* dx, const b200_conv_geom* g, const void* residual, void* stream);
@@ -254,6 +259,46 @@ int b200_conv_dgrad_add(const void* dy, const void* w, void* dx, const b200_conv
    ~60 % of the SMs), > 0 = cap on the number of splits, < 0 = use -max_splits percent of the SMs (nothing runs alongside) */
 int b200_conv_wgrad(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits,
                     void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * fp32 activation variants.  Every entry point above that reads or writes activations exists a second time with the
+ * suffix _f32 and the same argument list: activations, residuals, conv / linear weights and their outputs are then NHWC
+ * (or [M][K]) fp32 instead of bf16, convolutions and linear layers run tcgen05.mma kind::tf32 (fp32 operands, the tensor
+ * core multiplies their top 19 bits, fp32 accumulation), everything else computes in fp32 as before.  This is the
+ * precision of the reference's own training run (fp32 model, cuDNN TF32 convolutions, no autocast:
+ * notebooks/code/cifar10-distributed-smddp-gpu.py:145,155-168).  b200_augment writes fp32 NHWC with layout == 2.
+ * ------------------------------------------------------------------------------------------- */
+int b200_conv_fwd_f32(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g, int relu, void* stream);
+int b200_conv_fwd_stats_f32(const void* x, const void* w, void* y, const b200_conv_geom* g, float* bn_sums, void* stream);
+int b200_conv_dgrad_f32(const void* dy, const void* w, void* dx, const b200_conv_geom* g, void* stream);
+int b200_conv_dgrad_add_f32(const void* dy, const void* w, void* dx, const b200_conv_geom* g, const void* residual, void* stream);
+int b200_conv_wgrad_f32(const void* x, const void* dy, float* dw, const b200_conv_geom* g, int max_splits, void* stream);
+int b200_bn_stats_f32(const void* x, size_t rows, int C, const float* gamma, const float* beta, float eps, float momentum,
+                      float* stat, float* running_mean, float* running_var, void* scratch, size_t scratch_bytes, void* stream);
+int b200_bn_apply_f32(const void* x, const void* residual, void* y, size_t rows, int C, const float* stat, int relu, void* stream);
+int b200_bn_apply_sums_f32(const void* x, const void* residual, void* y, size_t rows, int C, float* sums, const float* gamma,
+                           const float* beta, float eps, float momentum, float* stat, float* running_mean, float* running_var,
+                           int relu, void* stream);
+int b200_bn_apply_sums_keep_f32(const void* x, const void* residual, void* y, size_t rows, int C, float* sums, const float* gamma,
+                                const float* beta, float eps, float momentum, float* stat, float* running_mean,
+                                float* running_var, int relu, void* stream);
+int b200_bn_bwd_reduce_f32(const void* dy, const void* x, const void* y, size_t rows, int C, const float* stat, int relu,
+                           float* sums, float* dgamma, float* dbeta, float beta_accum, void* scratch, size_t scratch_bytes,
+                           void* stream);
+int b200_bn_bwd_apply_f32(const void* dy, const void* x, const void* y, void* dx, void* dres, size_t rows, int C,
+                          const float* stat, const float* sums, int relu, void* stream);
+int b200_bn_fwd_fused_f32(const void* x, const void* residual, void* y, size_t rows, int C, const float* gamma, const float* beta,
+                          float eps, float momentum, float* stat, float* running_mean, float* running_var, int relu, void* stream);
+size_t b200_bn_bwd_fused_max_rows_f32(void);
+int b200_bn_bwd_fused_f32(const void* dy, const void* x, const void* y, void* dx, void* dres, size_t rows, int C, const float* stat,
+                          int relu, float* dgamma, float* dbeta, float beta_accum, void* stream);
+int b200_maxpool_fwd_f32(const void* x, void* y, uint8_t* argmax, int N, int H, int W, int C, int k, int stride, int pad, void* stream);
+int b200_maxpool_bwd_f32(const void* dy, const uint8_t* argmax, void* dx, int N, int H, int W, int C, int k, int stride, int pad,
+                         void* stream);
+int b200_avgpool_fwd_f32(const void* x, void* y, int N, int HW, int C, void* stream);
+int b200_avgpool_bwd_f32(const void* dy, void* dx, int N, int HW, int C, void* stream);
+int b200_relu_bwd_f32(const void* dy, const void* y, void* dx, size_t n, void* stream);
+int b200_colsum_accum_f32(const void* dy, size_t rows, int C, int c_valid, float* out, void* stream);
 
 /* ---- sequence models of the trojan-detection zoo (csrc/seq.cu), fp32 ---- */
 /* C[m][n] = sum_k A[m*sam + k*sak] * B[k*sbk + n*sbn] (+ bias[n]) (+ beta*C) (optional ReLU); transposes are strides */

@@ -304,3 +304,35 @@ def test_mntd_zoo_trainer_and_meta_classifier_on_gpu(task, tmp_path):
     auc = run_meta.run(task, "M", gpu=True, shadow_root=root, save_root=str(tmp_path / "meta"), n_repeat=1, n_epoch=1,
                        train_num=1, val_num=1, test_num=2, verbose=False)
     assert 0.0 <= auc <= 1.0
+
+
+def test_pooled_bn_statistics_match_per_layer_finalize(pg, monkeypatch):
+    """TrainStep keeps every conv-epilogue BN-statistics buffer in one pool (one memset per step, scale/shift derived inside
+    the apply kernel); without the pool each layer runs its own finalize kernel.  Same math: same losses, fewer launches."""
+    from b200ddp.models import get_model
+    from b200ddp.nn import CrossEntropyLoss
+    from b200ddp.ops import _lib as L
+    from b200ddp.ops import optim as boptim
+    from b200ddp.runtime.engine import TrainStep
+    dev = _dev()
+    pg.set_compute_dtype("fp32")
+    try:
+        xs = torch.randint(0, 256, (3, 64, 32, 32, 3), dtype=torch.uint8).pin_memory()
+        ys = torch.randint(0, 10, (3, 64)).pin_memory()
+        out = {}
+        for pooled in ("1", "0"):
+            monkeypatch.setenv("B200DDP_POOL_BN_SUMS", pooled)
+            torch.manual_seed(3)
+            net = pg.DistributedDataParallel(get_model("resnet18").to(dev))
+            opt = boptim.SGD(net.parameters(), lr=0.01, momentum=0.9)
+            step = TrainStep(net, CrossEntropyLoss(), opt, 64, device=dev, graph=False, seed=5, augment=False)
+            c0 = L.LAUNCHES[0]
+            losses = [step(xs[i], ys[i], need_loss=True) for i in range(3)]
+            out[pooled] = (losses, (L.LAUNCHES[0] - c0) // 3, net.module.bn1.running_mean.clone())
+        (l1, n1, rm1), (l0, n0, rm0) = out["1"], out["0"]
+        assert abs(l1[0] - l0[0]) < 1e-3 * max(1.0, abs(l0[0])), (l1, l0)
+        assert abs(l1[1] - l0[1]) < 0.1 * max(1.0, abs(l0[1])), (l1, l0)
+        assert torch.allclose(rm1, rm0, rtol=1e-3, atol=1e-4)
+        assert n1 < n0, (n1, n0)
+    finally:
+        pg.set_compute_dtype("bf16")
