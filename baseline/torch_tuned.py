@@ -12,7 +12,9 @@ Modes (all: global batch / world per rank, same step count, CUDA-event timing, L
 max over ranks):
   ``fp32``         fp32 weights and activations, torch defaults (cuDNN may use TF32 for convolutions), eager
   ``fp32_graph``   the same step captured in a CUDA graph, channels_last
-  ``bf16_graph``   ``torch.autocast(bfloat16)`` + channels_last + CUDA graph (the tuned-PyTorch ceiling)
+  ``bf16``         ``torch.autocast(bfloat16)`` + channels_last, eager
+  ``bf16_graph``   ``torch.autocast(bfloat16)`` + channels_last + CUDA graph (the tuned-PyTorch ceiling on one GPU; with DDP
+                   over several GPUs the captured step measured SLOWER than eager on this box, so both are reported)
 
 None of this repo's kernels, models or engine is on this path (only ``torch`` / ``torchvision``).
 """
@@ -63,7 +65,7 @@ def run_mode(mode: str, model_name: str, per_rank: int, hw: int, steps: int, war
     bf16 = mode.startswith("bf16")
     torch.manual_seed(1)
     model = _build(model_name, hw).to(dev)
-    if use_graph:
+    if use_graph or bf16:
         model = model.to(memory_format=torch.channels_last)
     if world > 1:
         model = nn.parallel.DistributedDataParallel(model, device_ids=[dev.index], process_group=group)
@@ -78,7 +80,7 @@ def run_mode(mode: str, model_name: str, per_rank: int, hw: int, steps: int, war
 
     def body():
         inp = _augment(sx, so, mean, inv_std)
-        if use_graph:
+        if use_graph or bf16:
             inp = inp.contiguous(memory_format=torch.channels_last)
         opt.zero_grad(set_to_none=True)
         with torch.autocast("cuda", dtype=torch.bfloat16, enabled=bf16):
@@ -168,7 +170,7 @@ def run_mode(mode: str, model_name: str, per_rank: int, hw: int, steps: int, war
 
 
 def run_all(model_name: str, per_rank: int, hw: int, steps: int, warmup: int, xs, ys, offs, world: int,
-            device: torch.device, modes=("fp32", "fp32_graph", "bf16_graph")) -> Dict:
+            device: torch.device, modes=("fp32", "fp32_graph", "bf16", "bf16_graph")) -> Dict:
     """Every mode, each inside its own try block: the comparison must never take the product's bench line down."""
     group = None
     if world > 1:
@@ -197,7 +199,7 @@ def _new_group_takes_device_id() -> bool:
 
 
 def run(gpus: int, steps: int, warmup: int, global_batch: int = 256, model_name: str = "resnet18",
-        modes=("fp32", "fp32_graph", "bf16_graph")) -> dict:
+        modes=("fp32", "fp32_graph", "bf16", "bf16_graph")) -> dict:
     """Stand-alone entry (``bench.py --impl torch_tuned``): own NCCL process group from the torchrun env."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

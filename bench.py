@@ -220,7 +220,7 @@ def main():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-like-for-like", action="store_true")
     ap.add_argument("--no-secondary", action="store_true")
-    ap.add_argument("--lfl-modes", type=str, default="fp32,fp32_graph,bf16_graph", help="stock-PyTorch modes to measure alongside")
+    ap.add_argument("--lfl-modes", type=str, default="fp32,fp32_graph,bf16,bf16_graph", help="stock-PyTorch modes to measure alongside")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     if args.impl in ("reference", "reference_on_b200", "torch_tuned"):

@@ -14,7 +14,7 @@ fi
 timeout 600 $TR --master-port 29701 bench.py --gpus $N --steps 100 --warmup 5 > gpurun_out/r2f_bench_fp32_$N.log 2>&1; echo "bench fp32 rc=$?" | tee -a $RC
 B200DDP_FUSED_SGD=0 timeout 600 $TR --master-port 29702 bench.py --gpus $N --steps 100 --warmup 5 --no-like-for-like --no-secondary > gpurun_out/r2f_bench_fp32_unfused_$N.log 2>&1; echo "bench fp32 unfused rc=$?" | tee -a $RC
 timeout 600 $TR --master-port 29703 bench.py --gpus $N --steps 100 --warmup 5 --dtype bf16 --no-like-for-like --no-secondary > gpurun_out/r2f_bench_bf16_$N.log 2>&1; echo "bench bf16 rc=$?" | tee -a $RC
-timeout 900 $TR --master-port 29704 bench.py --gpus $N --model resnet50 --dtype bf16 --global-batch $((128*N)) --steps 10 --warmup 3 --lfl-modes fp32,bf16_graph > gpurun_out/r2f_r50_bf16_$N.log 2>&1; echo "r50 rc=$?" | tee -a $RC
+timeout 900 $TR --master-port 29704 bench.py --gpus $N --model resnet50 --dtype bf16 --global-batch $((128*N)) --steps 10 --warmup 3 --lfl-modes fp32,bf16,bf16_graph > gpurun_out/r2f_r50_bf16_$N.log 2>&1; echo "r50 rc=$?" | tee -a $RC
 timeout 600 $TR --master-port 29705 bench.py --impl reference --gpus $N --steps 20 --warmup 3 > gpurun_out/r2f_ref_$N.log 2>&1; echo "reference rc=$?" | tee -a $RC
 timeout 600 $TR --master-port 29706 bench.py --impl reference_on_b200 --gpus $N --steps 20 --warmup 3 > gpurun_out/r2f_ref_on_b200_$N.log 2>&1; echo "reference_on_b200 rc=$?" | tee -a $RC
 for f in bench_fp32 bench_fp32_unfused bench_bf16 r50_bf16 ref ref_on_b200; do grep '^{' gpurun_out/r2f_${f}_$N.log | tail -n 1 | python -c "
