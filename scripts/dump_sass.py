@@ -5,11 +5,12 @@ import collections, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OUT = os.path.join(ROOT, "profiles", "sass")
 os.makedirs(OUT, exist_ok=True)
-REPRESENTATIVE = {"conv_tc": ["conv_tc_kernelILi0ELi128ELi4", "conv_tc_kernelILi2ELi128ELi4"], "comm": ["allreduce_shard_kernelILi0ELi8ELi8ELb1", "allreduce_oneshot_kernelILi0ELi8ELi2"],
-                  "bn": ["bn_stats_kernel", "bn_bwd_reduce_kernelILb1"], "net_mega": ["net_fwd_bwd_kernel"], "seq": ["lstm_rec_fwd_kernel", "mel_frontend_kernel"], "loss": ["softmax_xent_kernelI13__nv_bfloat16"], "optim": ["sgd_kernelILb1ELb1ELb0"], "pool": ["augment_kernel"]}
+REPRESENTATIVE = {"conv_tc": ["conv_tc_kernelIfLi0ELi128ELi4", "conv_tc_kernelIfLi2ELi128ELi4", "conv_tc_kernelI13__nv_bfloat16Li0ELi128ELi4", "conv_tc_kernelI13__nv_bfloat16Li2ELi128ELi4"],
+                  "comm": ["allreduce_sgd_shard_kernelILi8ELi4ELb1", "allreduce_shard_kernelILi0ELi8ELi8ELb1", "allreduce_oneshot_kernelILi0ELi8ELi2"],
+                  "bn": ["bn_stats_kernelI13__nv", "bn_bwd_reduce_kernelIfLb1", "bn_apply_sums_kernelIfLb1ELb0"], "net_mega": ["net_fwd_bwd_kernel"], "seq": ["lstm_rec_fwd_kernel", "mel_frontend_kernel"], "loss": ["softmax_xent_kernelIf"], "optim": ["sgd_kernelILb1ELb1ELb0"], "pool": ["augment_kernel"]}
 KEY = re.compile(r"FFMA|ACQBULK|PREEXIT|UTC\w*MMA\S*|LDTM\S*|STTM\S*|UTMALDG\S*|UTMASTG\S*|UBLKCP\S*|LDGSTS\S*|LDGMC\S*|SYNCS\S*|UTCBAR\S*|UTCATOM\S*|RED\.\S*|REDG\S*|ATOMG\S*|MEMBAR\S*|UCGABAR\S*|HMMA\S*|LDG\.E\.128\S*|STG\.E\.128\S*|CCTL\S*|MAPA\S*|LD\.E\S*|LDS\S*")
 summary = ["# SASS evidence (cuobjdump -sass of build/*.o, sm_100a)\n",
-           "Tensor-core path: `UTCHMMA` = tcgen05.mma, `LDTM` = tcgen05.ld, `UTCBAR` = tcgen05.commit, `UTMALDG` = TMA tile load (cp.async.bulk.tensor),",
+           "Tensor-core path: `UTCHMMA` = tcgen05.mma (kind::f16 and kind::tf32 instances), `LDTM` = tcgen05.ld, `UTCBAR` = tcgen05.commit, `UTMALDG` = TMA tile load (cp.async.bulk.tensor),",
            "`LDGSTS` = cp.async, `SYNCS` = mbarrier, `UCGABAR` = cluster barrier.  NVLink path: `LDGMC.*ADD` = multimem.ld_reduce,",
            "`ST/STG.*STRONG.SYS` = peer / multicast stores, `LDG.*STRONG.SYS` = peer loads and flag polls.  No `HMMA` (legacy mma.sync) anywhere.",
            "Programmatic dependent launch: `PREEXIT` = griddepcontrol.launch_dependents, `ACQBULK` = griddepcontrol.wait.\n"]
