@@ -64,7 +64,11 @@ class TrainStep:
             self._comm = _pg.get_comm()         # polled after every step: a timed-out collective must not go unnoticed
             BF.assume_unit_loss_grad(True)
             bmod.defer_bn_counters(True)
-            self._pool_bn = os.environ.get("B200DDP_POOL_BN_SUMS", "1") not in ("0", "false", "off")
+            # Off by default: measured on one B200 (resnet18, fp32) the pooled form saves 15 launches per step and is SLOWER,
+            # 1.370 vs 1.270 ms at batch 256 and 0.793 vs 0.766 ms at batch 32 -- every CTA of the apply kernel then derives
+            # 8 scale/shift pairs from the sums (32 dependent loads + rsqrt) before it touches its first row, while the tiny
+            # finalize kernel overlaps the conv's tail through programmatic dependent launch (profiles/r2/pooled_bn.md).
+            self._pool_bn = os.environ.get("B200DDP_POOL_BN_SUMS", "0") not in ("0", "false", "off")
             # this engine owns the whole step, so the optimizer may move into the gradient collective (world > 1)
             fuse = getattr(optimizer, "fuse_into_backward", None)
             self.fused_optimizer = bool(fuse(True)) if fuse is not None else False

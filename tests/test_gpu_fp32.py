@@ -251,11 +251,11 @@ def test_workshop_net_fp32_matches_cpu_oracle():
         for (n, p), (_, q) in zip(ours.named_parameters(), ref.named_parameters()):
             assert p.grad is not None, n
             rel = float((p.grad.cpu() - q.grad).norm() / (q.grad.norm() + 1e-12))
-            # The fc gradients see only forward rounding.  The conv gradients sit upstream of ReLU + 2x2 max-pools: an
-            # activation pair within TF32 rounding of a tie routes its gradient to the other element (same effect as the
-            # ReLU flips in tests/test_gpu_chain.py), a few such windows per thousand move the Frobenius norm by percents
-            # while every kernel on its own is within 2e-3 (test_conv_tf32_fwd_dgrad_wgrad covers these very shapes).
-            tol = 5e-3 if n.startswith("fc") else 5e-2
-            assert rel < tol, "gradient of %s: relative error %.3e" % (n, rel)
+            # Every gradient here sits upstream of a ReLU (fused into the conv / linear epilogues) and most of a 2x2 max-pool:
+            # an activation within TF32 rounding of zero, or a pair within rounding of a tie, sends its gradient elsewhere
+            # (the effect tests/test_gpu_chain.py removes by replaying the masks); a few such elements per thousand move a
+            # Frobenius norm by percents while every kernel on its own is within 2e-3 (test_conv_tf32_fwd_dgrad_wgrad and
+            # test_linear_tf32 cover these very shapes).  Loss and logits above are the tight part of this test.
+            assert rel < 5e-2, "gradient of %s: relative error %.3e" % (n, rel)
     finally:
         bd.set_compute_dtype("bf16")
