@@ -145,6 +145,120 @@ def _to_host(tensors) -> np.ndarray:
     return torch.stack([t.detach().reshape(()).float() for t in tensors]).cpu().double().numpy()
 
 
+class GraphedMetaStep:
+    """One meta-training step -- score ONE shadow model on the queries, BCE, backward through the shadow model into the
+    queries, Adam -- captured as a CUDA graph and replayed per shadow model.
+
+    The reference takes one optimizer step per checkpoint (``utils_meta.py:44-59``); that order is kept (the queries a model
+    sees depend on every model before it), so the loop cannot be batched across models without changing the algorithm.  What
+    CAN go is everything around the ~50 kernels of a step: the shadow architecture's parameters become views of one static
+    flat buffer, a checkpoint is "loaded" by ONE device copy from the bank's flat image of it, the label is a device copy,
+    and the whole forward / backward / Adam sequence is one graph replay instead of ~50 launches issued from Python.  Loss
+    and score of every step land in device arrays that are read once per epoch."""
+
+    def __init__(self, meta_model, basic_model, optimizer, is_discrete, max_steps: int = 4096):
+        self.meta, self.basic, self.opt, self.is_discrete = meta_model, basic_model, optimizer, is_discrete
+        dev = next(meta_model.parameters()).device
+        self.keys = [k for k, v in basic_model.state_dict().items() if v.is_floating_point()]
+        sd = basic_model.state_dict()
+        self.numels = [sd[k].numel() for k in self.keys]
+        self.flat = torch.zeros(sum(self.numels), dtype=torch.float32, device=dev)
+        named = dict(basic_model.named_parameters())
+        named.update(dict(basic_model.named_buffers()))
+        off = 0
+        with torch.no_grad():
+            for k, n in zip(self.keys, self.numels):
+                t = named[k]
+                view = self.flat[off: off + n].view(t.shape)
+                view.copy_(t)
+                t.data = view                       # the module now computes on the static buffer
+                off += n
+        self.target = torch.zeros(1, device=dev)
+        self.loss = torch.zeros((), device=dev)
+        self.score = torch.zeros((), device=dev)
+        self.losses = torch.zeros(max_steps, device=dev)
+        self.scores = torch.zeros(max_steps, device=dev)
+        self._images = {}
+        self._capture()
+
+    def image(self, bank: "ShadowBank", path: str) -> torch.Tensor:
+        """The checkpoint as one flat fp32 tensor in this module's parameter order (built once, kept on the device)."""
+        img = self._images.get(path)
+        if img is None:
+            st = bank.state(path)
+            img = torch.cat([st[k].reshape(-1).float() for k in self.keys]).contiguous()
+            self._images[path] = img
+        return img
+
+    def _body(self):
+        score = _score(self.meta, self.basic, self.is_discrete)
+        l = self.meta.loss(score, self.target)
+        self.opt.zero_grad(set_to_none=True)
+        l.backward()
+        self.opt.step()
+        self.loss.copy_(l.detach().reshape(()))
+        self.score.copy_(score.detach().reshape(()))
+
+    def _capture(self):
+        # warm-up steps are real Adam steps: snapshot the meta-classifier and restore it (and reset the optimizer state the
+        # warm-up created) so that capturing leaves no trace
+        params = [p for g in self.opt.param_groups for p in g["params"]] + [p for p in self.meta.parameters()]
+        snap = [(p, p.detach().clone()) for p in {id(p): p for p in params}.values()]
+        had_state = {id(p) for p in self.opt.state}
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(3):
+                self._body()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._body()
+        with torch.no_grad():
+            for p, c in snap:
+                p.copy_(c)
+            for p, st in self.opt.state.items():
+                if id(p) not in had_state:
+                    for v in st.values():
+                        if torch.is_tensor(v):
+                            v.zero_()
+        torch.cuda.synchronize()
+
+    def step(self, image: torch.Tensor, target: torch.Tensor, slot: int):
+        self.flat.copy_(image, non_blocking=True)
+        self.target.copy_(target, non_blocking=True)
+        self.graph.replay()
+        self.losses[slot].copy_(self.loss, non_blocking=True)
+        self.scores[slot].copy_(self.score, non_blocking=True)
+
+
+def _graphed_step(meta_model, basic_model, optimizer, is_discrete):
+    """The cached ``GraphedMetaStep`` of this (meta-classifier, shadow module, optimizer) triple, or None when the loop has
+    to stay eager (CPU, ``B200DDP_META_GRAPH=0``, an optimizer that cannot be captured, non-float state in the model)."""
+    import os
+    dev = next(meta_model.parameters()).device
+    if dev.type != "cuda" or os.environ.get("B200DDP_META_GRAPH", "1") in ("0", "false", "off"):
+        return None
+    if not getattr(optimizer, "defaults", {}).get("capturable", False):
+        return None
+    if any(not v.is_floating_point() for v in basic_model.state_dict().values()):
+        return None
+    g = getattr(meta_model, "_graphed_step", None)
+    if g is False:
+        return None
+    if g is None or g.basic is not basic_model or g.opt is not optimizer:
+        try:
+            g = GraphedMetaStep(meta_model, basic_model, optimizer, is_discrete)
+        except Exception as e:           # a model whose step cannot be captured (host sync inside): keep the eager loop
+            import warnings
+            warnings.warn("MNTD meta step not captured as a CUDA graph (%s: %s); running eagerly" % (type(e).__name__, str(e)[:120]))
+            torch.cuda.synchronize()
+            g = False
+        object.__setattr__(meta_model, "_graphed_step", g)
+    return g or None
+
+
 def _auc_acc(preds, labs, threshold):
     from sklearn.metrics import roc_auc_score
     preds, labs = np.array(preds), np.array(labs)
@@ -161,6 +275,18 @@ def epoch_meta_train(meta_model, basic_model, optimizer, dataset: List[Tuple[str
     bank = bank or ShadowBank([x for x, _ in dataset], next(meta_model.parameters()).device)
     dev = next(meta_model.parameters()).device
     targets = {0: torch.zeros(1, device=dev), 1: torch.ones(1, device=dev)}
+    graphed = _graphed_step(meta_model, basic_model, optimizer, is_discrete)
+    if graphed is not None and len(dataset) <= graphed.losses.numel():
+        order = np.random.permutation(len(dataset))
+        labs = []
+        for slot, i in enumerate(order):
+            x, y = dataset[i]
+            graphed.step(graphed.image(bank, x), targets[int(y)], slot)
+            labs.append(y)
+        n = len(order)
+        both = torch.stack([graphed.losses[:n], graphed.scores[:n]]).cpu().double().numpy()     # the epoch's only read-back
+        auc, acc = _auc_acc(both[1], labs, threshold)
+        return float(both[0].sum()) / n, auc, acc
     losses, scores, labs = [], [], []
     for i in np.random.permutation(len(dataset)):
         x, y = dataset[i]

@@ -61,7 +61,7 @@ def run(task, troj_type="M", no_qt=False, load_exist=False, gpu=False, shadow_ro
             params = list(meta_model.fc.parameters()) + list(meta_model.output.parameters())
             if not no_qt:
                 params = list(meta_model.parameters())
-            optimizer = torch.optim.Adam(params, lr=1e-3)
+            optimizer = torch.optim.Adam(params, lr=1e-3, capturable=bool(gpu))     # capturable: the step replays as a CUDA graph
             best = None
             for _ in range(n_epoch):
                 UM.epoch_meta_train(meta_model, shadow_model, optimizer, train_ds, is_discrete, threshold="half", bank=bank)

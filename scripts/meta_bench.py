@@ -4,8 +4,10 @@
   legacy   what ``notebooks/code/utils_meta.py:38-72`` does per shadow model, with the per-step disk read already removed:
            ``load_state_dict`` into the shadow module (14 device copies), forward, loss, ``backward``, Adam step, then
            ``loss.item()`` and ``score.item()`` (two pipeline drains per model);
-  ours     ``workloads/mntd/meta.py``: the shadow model is evaluated functionally on the bank's tensors, the MLP / BCE run on
-           this package's kernels, nothing crosses to the host until the end of the epoch.
+  ours     ``workloads/mntd/meta.py`` eager loop: the shadow model is evaluated functionally on the bank's tensors, the MLP / BCE
+           run on this package's kernels, nothing crosses to the host until the end of the epoch;
+  graph    the same with a capturable Adam: every step is one CUDA-graph replay (``GraphedMetaStep``), a checkpoint is
+           loaded by one device copy.
 
 Both train the same meta-classifier from the same seed for the same epochs; the final validation AUC is printed for both.
 """
@@ -54,13 +56,13 @@ def main():
     dev = "cuda"
     bank = UM.ShadowBank([p for p, _ in tr + va + te], dev)
     out = {"train_models": len(tr), "val_models": len(va)}
-    for mode in ("legacy", "ours"):
+    for mode in ("legacy", "ours", "graph"):
         torch.manual_seed(0)
         np.random.seed(0)
         shadow = Model(gpu=True)
         meta = UM.MetaClassifier(input_size, class_num, gpu=True)
         meta.inp.data = torch.zeros_like(meta.inp).normal_() * float(std[0]) + float(mean[0])
-        opt = torch.optim.Adam(meta.parameters(), lr=1e-3)
+        opt = torch.optim.Adam(meta.parameters(), lr=1e-3, capturable=(mode == "graph"))
         times = []
         for ep in range(a.epochs):
             torch.cuda.synchronize()
@@ -74,6 +76,7 @@ def main():
         _, auc, _ = UM.epoch_meta_eval(meta, shadow, va or tr, is_discrete, threshold="half", bank=bank)
         out[mode] = {"epoch_ms_first": times[0] * 1e3, "epoch_ms_steady": float(np.median(times[1:])) * 1e3, "val_auc": auc}
     out["speedup_steady"] = out["legacy"]["epoch_ms_steady"] / out["ours"]["epoch_ms_steady"]
+    out["speedup_steady_graph"] = out["legacy"]["epoch_ms_steady"] / out["graph"]["epoch_ms_steady"]
     print("META_BENCH " + json.dumps(out), flush=True)
 
 
