@@ -72,9 +72,17 @@ def ptr(t) -> c_void_p:
     return c_void_p(t.data_ptr())
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr(stream=None) -> c_void_p:
-    s = stream if stream is not None else torch.cuda.current_stream()
-    return c_void_p(s.cuda_stream)
+    """The launch stream as a ``cudaStream_t``.  Called once per native op: the current stream is read through torch's raw
+    accessor (0.2 us) rather than by building a ``torch.cuda.Stream`` object (2 us) -- the eager path is host-bound."""
+    if stream is not None:
+        return c_void_p(stream.cuda_stream)
+    if _raw_stream is not None:
+        return c_void_p(_raw_stream(torch.cuda.current_device()))
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
 def dtype_code(dt: torch.dtype) -> int:
