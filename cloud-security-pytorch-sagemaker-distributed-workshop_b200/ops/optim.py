@@ -124,6 +124,33 @@ class SGD(_FusedBase):
     def flat_state(self):
         return {i: m for i, m in enumerate(self._momentum_flat.values())}
 
+    @torch.no_grad()
+    def sync_state(self):
+        """Collective (every rank calls it): make each rank's momentum buffer complete.  With the optimizer folded into the
+        bucket collectives a rank only ever updates the momentum of the shards it owns -- the rest of its buffer still holds
+        the initial zeros -- so the full state is the SUM over ranks.  Call before writing a checkpoint meant for resume
+        (``workloads/cifar10_train.py`` does); afterwards every rank holds the whole state and training can go on as it was
+        (the fused kernel reads and writes its own shards only)."""
+        from ..parallel import process_group as pg
+        for o in self._flat_owners:
+            if id(o) in self._fused_key and o.world_size > 1:
+                m = self._momentum_flat.get(id(o))
+                if m is not None:
+                    # a shard that ANOTHER rank owns has not been written here since the last sync: zero it first, so that a
+                    # second sync_state() does not add the same shards twice
+                    self._zero_unowned(o, m)
+                    pg.all_reduce(m)
+
+    def _zero_unowned(self, o, m):
+        world, rank = o.world_size, o.rank
+        for b in o.buckets:
+            chunks = b.numel // 4
+            per = (chunks + world - 1) // world
+            lo, hi = min(rank * per, chunks) * 4, min((rank + 1) * per, chunks) * 4
+            seg = m[b.start: b.start + b.numel]
+            seg[:lo].zero_()
+            seg[hi:].zero_()
+
 
 class Adam(_FusedBase):
     def __init__(self, params: Iterable, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,

@@ -63,7 +63,7 @@ def save_full(model: nn.Module, optimizer, epoch: int, path: str, extra: Optiona
 
 
 def load_full(model: nn.Module, optimizer, path: str) -> int:
-    blob = torch.load(path, map_location="cpu", weights_only=False)
+    blob = torch.load(path, map_location="cpu", weights_only=True)      # tensors, lists, dicts and numbers only
     unwrap(model).load_state_dict(blob["model"])
     if hasattr(model, "refresh_shadow"):
         model.refresh_shadow()

@@ -170,6 +170,8 @@ def train(cfg: TrainConfig):
         comm = bd.get_comm()
         if comm is not None:
             comm.check_health()
+    if cfg.save_full_checkpoint and hasattr(optimizer, "sync_state"):
+        optimizer.sync_state()        # collective: with the optimizer inside the collectives each rank holds its shards' momentum
     logger.info("Saving trained model only on rank 0")
     if rank == 0:
         logger.info("Saving the model.")

@@ -287,3 +287,23 @@ def test_trainer_saves_full_checkpoint_and_resumes(tmp_path, monkeypatch):
     assert all(torch.equal(w1[k], v) for k, v in m2.state_dict().items())
     m3 = train(parse_args(common + ["--epochs", "2", "--resume", str(ck)]))       # one more epoch from the restored state
     assert any(not torch.equal(w1[k], v) for k, v in m3.state_dict().items())
+
+
+def test_sgd_sync_state_shard_ownership_matches_the_fused_kernel():
+    """``SGD._zero_unowned`` keeps exactly the range ``allreduce_sgd_shard_kernel`` (csrc/comm.cu) updates on this rank:
+    16-byte chunks split as ceil(chunks / world) per rank, per bucket; summed over ranks every element is kept once."""
+    from types import SimpleNamespace
+    from b200ddp.ops.optim import SGD
+    buckets = [SimpleNamespace(start=0, numel=40), SimpleNamespace(start=40, numel=4), SimpleNamespace(start=44, numel=100)]
+    for world in (2, 3, 8):
+        total = torch.zeros(144)
+        for rank in range(world):
+            m = torch.ones(144)
+            SGD._zero_unowned(None, SimpleNamespace(world_size=world, rank=rank, buckets=buckets), m)
+            total += m
+            for b in buckets:
+                chunks = b.numel // 4
+                per = -(-chunks // world)
+                lo, hi = min(rank * per, chunks) * 4, min((rank + 1) * per, chunks) * 4
+                assert float(m[b.start + lo: b.start + hi].sum()) == hi - lo
+        assert torch.equal(total, torch.ones(144)), world
