@@ -165,6 +165,7 @@ def run(gpus: int, steps: int, warmup: int, global_batch: int = 256, model_type:
         ms = bd.max_over_ranks(ms)
         rank = bd.get_rank()
         native = [L.LAUNCHES[0]]
+        from b200ddp.runtime.graphed import STATS as graph_stats
         comm = bd.get_comm()
         if comm is not None:
             comm.check_health()
@@ -184,6 +185,7 @@ def run(gpus: int, steps: int, warmup: int, global_batch: int = 256, model_type:
             "kernels + NVLink all-reduce under the script's own PIL loader, loop and optim.SGD (loader inside the timed region)"
             if on_b200 else
             "unmodified reference script; torch DDP+NCCL; PIL dataloader num_workers=0 inside the timed region")
+    extra = {"graphed_forward_backward": dict(graph_stats)} if on_b200 else {}
     return {"impl": impl, "rank": rank, "metric": "images/sec", "value": value, "unit": "images/sec",
             "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "fp32", "data": "synthetic",
@@ -191,4 +193,4 @@ def run(gpus: int, steps: int, warmup: int, global_batch: int = 256, model_type:
                     "h2d_bytes_per_step": (global_batch // world) * (3 * 32 * 32 * 4 + 8), "d2h_bytes_per_step": 0},
             "gpu_launches": native[0] if native else 0,
             "config": {"model": label, "global_batch": global_batch,
-                       "seq_len": None, "parallelism": "dp%d" % world, "note": note}}
+                       "seq_len": None, "parallelism": "dp%d" % world, "note": note, **extra}}

@@ -46,7 +46,8 @@ class DistributedDataParallel(nn.Module):
     def __init__(self, module: nn.Module, device_ids=None, output_device=None, dim: int = 0,
                  broadcast_buffers: bool = True, process_group=None, bucket_cap_mb: Optional[float] = None,
                  find_unused_parameters: bool = False, gradient_as_bucket_view: bool = True,
-                 static_graph: bool = True, direct_grad_sink: bool = True, shadow_dtype="auto"):
+                 static_graph: bool = True, direct_grad_sink: bool = True, shadow_dtype="auto",
+                 graph_forward_backward: Optional[bool] = None):
         super().__init__()
         self.module = module
         self.broadcast_buffers = broadcast_buffers
@@ -158,6 +159,15 @@ class DistributedDataParallel(nn.Module):
             if self.flat_buffers is not None:
                 pg.broadcast(self.flat_buffers, src=0)
             self.refresh_shadow()
+        # ---- optional: model(x) / loss.backward() of a caller-owned loop as two CUDA-graph replays (runtime/graphed.py)
+        if graph_forward_backward is None:
+            import os
+            graph_forward_backward = os.environ.get("B200DDP_GRAPH_FWD_BWD", "0") not in ("0", "false", "off")
+        self._graphed = None
+        if graph_forward_backward and self.device.type == "cuda":
+            from ..runtime.graphed import GraphedForwardBackward
+            self._graphed = GraphedForwardBackward(self)
+        self._param_versions = self._versions()
         if self.cfg.debug:
             sizes = ", ".join("%d B (%d tensors)" % (sum(numels[i] for i in b.param_ids) * 4, len(b.param_ids))
                               for b in buckets)
@@ -244,13 +254,35 @@ class DistributedDataParallel(nn.Module):
             self.flat_grads.zero_()
             self._arena_dirty = False
 
-    def forward(self, *args, **kwargs):
-        if torch.is_grad_enabled():
-            self._adopt_dropped_grads()
+    def _versions(self) -> int:
+        return sum(p._version for p in self.params) if self.flat_shadow is not None else 0
+
+    def _sync_shadow_after_foreign_step(self):
+        """The bf16 shadow weights are maintained by this package's fused optimizers.  Any other writer of the parameters
+        (``torch.optim``, ``p.data.add_``, ``load_state_dict`` on the inner module) bumps their version counters: re-derive
+        the shadow then, or the tensor-core kernels would keep computing with the old weights."""
+        if self.flat_shadow is not None and not torch.cuda.is_current_stream_capturing():
+            v = self._versions()
+            if v != self._param_versions:
+                self._param_versions = v
+                self.refresh_shadow()
+
+    def _forward_eager(self, *args, **kwargs):
         if (self.broadcast_buffers and self.world_size > 1 and self.flat_buffers is not None
                 and self.require_backward_grad_sync and self.training):
             pg.broadcast(self.flat_buffers, src=0)       # KB12: one coalesced broadcast
         return self.module(*args, **kwargs)
+
+    def forward(self, *args, **kwargs):
+        if torch.is_grad_enabled():
+            self._adopt_dropped_grads()
+        self._sync_shadow_after_foreign_step()
+        g = self._graphed
+        if g is not None and g.wants(args, kwargs):
+            return g(args[0])
+        if g is not None:
+            g.note_eager()
+        return self._forward_eager(*args, **kwargs)
 
     @contextlib.contextmanager
     def no_sync(self):

@@ -19,7 +19,9 @@ Importing this module makes those lines land on b200ddp, with the script byte-fo
   group is the b200 one; otherwise torch's own class is constructed.
 
 The script's own loop then runs on this framework: its ``optim.SGD`` steps the flat parameter arena through the views,
-``loss.backward()`` produces gradients with the tensor-core kernels and all-reduces the buckets over NVLink.
+``loss.backward()`` produces gradients with the tensor-core kernels and all-reduces the buckets over NVLink.  After the
+first full-size training batch ``model(data)`` and ``loss.backward()`` are one CUDA-graph replay each (forward; backward
+with the bucket collectives), everything else (evaluation, the last short batch) runs launch by launch.
 """
 from __future__ import annotations
 
@@ -84,6 +86,9 @@ class DistributedDataParallel(_TORCH_DDP, metaclass=_DDPMeta):
             kw = {k: v for k, v in kwargs.items() if k in allowed}
             for k, v in zip(allowed, args):
                 kw.setdefault(k, v)
+            # the script owns the loop (loss, optimizer): take what lies between model(data) and the gradients off the host
+            # as two CUDA-graph replays (b200ddp/runtime/graphed.py); B200DDP_SHIM_GRAPH=0 keeps every launch eager
+            kw["graph_forward_backward"] = os.environ.get("B200DDP_SHIM_GRAPH", "1") not in ("0", "false", "off")
             return _bd.DistributedDataParallel(_to_native(module), **kw)
         return _TORCH_DDP(module, *args, **kwargs)
 

@@ -46,5 +46,7 @@ sys.argv = [script, "--backend", "smddp", "--batch-size", "32", "--epochs", "1",
 runpy.run_path(script, run_name="__main__")
 import b200ddp as bd  # noqa: E402
 from b200ddp.ops import _lib as L  # noqa: E402
+from b200ddp.runtime.graphed import STATS  # noqa: E402
 print("NATIVE_LAUNCHES %d backend=%s dtype=%s" % (L.LAUNCHES[0], bd.get_backend(), bd.get_compute_dtype()), flush=True)
+print("GRAPHED " + json.dumps(STATS), flush=True)
 bd.destroy_process_group()

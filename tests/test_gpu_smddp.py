@@ -39,6 +39,11 @@ def test_reference_gpu_script_runs_unmodified_on_b200ddp(tmp_path, model_type):
     assert "Saving the model." in out
     line = [l for l in out.splitlines() if l.startswith("NATIVE_LAUNCHES")][-1]
     assert int(line.split()[1]) > 30 * 10 and "backend=b200" in line and "dtype=fp32" in line, line   # the native kernels ran
+    # 30 training batches of 32: model(data) / loss.backward() of the script's own loop ran as CUDA-graph replays
+    import json
+    stats = json.loads([l for l in out.splitlines() if l.startswith("GRAPHED ")][-1][len("GRAPHED "):])
+    assert stats["captures"] == 1 and stats["capture_failures"] == 0, (stats, out[-3000:])
+    assert stats["forward_replays"] == 30 and stats["backward_replays"] == 30, (stats, out[-3000:])
     sd = torch.load(str(tmp_path / "model.pth"), map_location="cpu", weights_only=True)
     assert all(k.startswith("module.") for k in sd)
     if model_type == "resnet18":
