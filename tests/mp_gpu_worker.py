@@ -168,6 +168,59 @@ def ddp():
     bd.get_comm().check_health()
 
 
+def graphed():
+    """The caller-owned loop of the reference script (zero_grad, model(data), torch's CrossEntropyLoss, backward, torch.optim.SGD)
+    on DistributedDataParallel(graph_forward_backward=True): the BN-buffer broadcast and the bucket collectives are inside the
+    two replayed graphs."""
+    from b200ddp.models import get_model
+    from b200ddp.runtime import graphed as G
+    from b200ddp.utils.ddp_check import grad_sync_check, params_identical
+    rank, world, dev = bd.get_rank(), bd.get_world_size(), bd.get_device()
+    bd.set_compute_dtype("fp32")
+    crit = torch.nn.CrossEntropyLoss()
+    for name, ncls in (("resnet18", 1000), ("custom", 10)):
+        torch.manual_seed(4321 + rank)
+        model = bd.DistributedDataParallel(get_model(name).to(dev), graph_forward_backward=True)
+        model.train()
+        B = 32
+        g = torch.Generator().manual_seed(99 + rank)          # every rank its own shard
+        xs = [torch.randn(B, 3, 32, 32, generator=g).to(dev) for _ in range(6)]
+        ys = [torch.randint(0, ncls, (B,), generator=g).to(dev) for _ in range(6)]
+
+        def fwd_bwd():
+            crit(model(xs[0]), ys[0]).backward()
+
+        before = dict(G.STATS)
+        res = grad_sync_check(model, fwd_bwd)                  # local pass under no_sync runs eagerly, the synced one is captured
+        st = {k: G.STATS[k] - before[k] for k in before}
+        check("%s graphed: captured, no failure" % name, st["captures"] == 1 and st["capture_failures"] == 0 and st["backward_replays"] == 1, str(st))
+        check("%s graphed: synced grads == mean(local grads)" % name, res["rel_err"] < 1e-5, "rel err %.2e" % res["rel_err"])
+        check("%s graphed: synced grads bitwise equal across ranks" % name, res["bitwise_equal"])
+        opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.9)
+        losses = []
+        for x, y in zip(xs, ys):
+            opt.zero_grad()
+            loss = crit(model(x), y)
+            loss.backward()
+            opt.step()
+            losses.append(float(loss.detach()))
+        torch.cuda.synchronize()
+        st = {k: G.STATS[k] - before[k] for k in before}
+        check("%s graphed: 6 more steps were replays" % name, st["forward_replays"] == 7 and st["backward_replays"] == 7 and st["captures"] == 1, str(st))
+        check("%s graphed: parameters identical across ranks after 6 steps" % name, params_identical(model))
+        check("%s graphed: losses finite" % name, all(v == v for v in losses), "%.3f -> %.3f" % (losses[0], losses[-1]))
+        if name == "resnet18":
+            # the per-forward buffer broadcast is inside graph F: one more replay on the SAME input everywhere puts every
+            # rank's running statistics in step with rank 0's (they differ after a forward on rank-specific shards)
+            same = torch.randn(B, 3, 32, 32, generator=torch.Generator().manual_seed(5)).to(dev)
+            model(same)
+            torch.cuda.synchronize()
+            bufs = gather_cpu(model.module.bn1.running_mean)
+            check("resnet18 graphed: BN buffers follow rank 0", all(torch.allclose(bufs[0], b, rtol=1e-5, atol=1e-6) for b in bufs[1:]))
+        del opt, model
+    bd.get_comm().check_health()
+
+
 def skip():
     comm = bd.get_comm()
     rank, world, dev = bd.get_rank(), bd.get_world_size(), bd.get_device()
@@ -196,7 +249,7 @@ def main():
     what = sys.argv[1]
     bd.init_process_group(backend="b200")
     try:
-        {"collectives": collectives, "ddp": ddp, "skip": skip}[what]()
+        {"collectives": collectives, "ddp": ddp, "graphed": graphed, "skip": skip}[what]()
     finally:
         if bd.get_rank() == 0:
             print("MP_GPU_RESULT " + json.dumps({"what": what, "world": bd.get_world_size(), "ok": all(RESULTS.values()) and bool(RESULTS),

@@ -51,6 +51,14 @@ def test_ddp_semantics_on_nvlink(world):
     assert v["checks"] >= 14
 
 
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_graphed_forward_backward_on_nvlink(world):
+    if world not in _worlds():
+        pytest.skip("needs %d GPUs" % world)
+    v = _run("graphed", world, 29670 + world)
+    assert v["checks"] >= 12
+
+
 def test_rank_that_skips_a_collective_is_detected():
     if 2 not in _worlds():
         pytest.skip("needs 2 GPUs")
