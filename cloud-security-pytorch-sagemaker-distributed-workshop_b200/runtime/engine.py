@@ -70,6 +70,8 @@ class TrainStep:
             # finalize kernel overlaps the conv's tail through programmatic dependent launch (profiles/r2/pooled_bn.md).
             self._pool_bn = os.environ.get("B200DDP_POOL_BN_SUMS", "0") not in ("0", "false", "off")
             # this engine owns the whole step, so the optimizer may move into the gradient collective (world > 1)
+            if getattr(model, "_graphed", None) is not None:
+                model._graphed.paused = True    # this engine replays the whole step: the model's own two graphs stay out of it
             fuse = getattr(optimizer, "fuse_into_backward", None)
             self.fused_optimizer = bool(fuse(True)) if fuse is not None else False
 
@@ -159,7 +161,10 @@ class TrainStep:
         torch.cuda.current_stream(self.device).wait_stream(s)
         torch.cuda.synchronize(self.device)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        # a model that can also replay its own forward/backward keeps its parameters' AccumulateGrad nodes on one stream
+        # (runtime/graphed.py): capture there, a captured backward cannot order itself against any other stream
+        own = getattr(getattr(self.model, "_graphed", None), "stream", None)
+        with torch.cuda.graph(g, stream=own):
             loss = self._body(self.static_x, self.static_y, self.static_off)
             self.static_loss.copy_(loss)
         self._graph = g

@@ -34,6 +34,10 @@ log = get_logger(__name__)
 STATS = {"captures": 0, "capture_failures": 0, "forward_replays": 0, "backward_replays": 0, "eager_forwards": 0}
 
 
+class _NotCapturable(RuntimeError):
+    """Raised during the (eager) warm-up: nothing has been captured yet, falling back is free of side effects."""
+
+
 class _Replay(torch.autograd.Function):
     @staticmethod
     def forward(ctx, anchor, gfb, x):
@@ -66,7 +70,9 @@ class GraphedForwardBackward:
     def __init__(self, ddp, warmup_iters: int = 3):
         self.ddp = ddp
         self.warmup_iters = int(warmup_iters)
-        self.enabled = True
+        self.enabled = True                    # False for good once a capture has failed
+        self.paused = False                    # a caller may route single calls to the eager path
+        self.failure = None                    # traceback of the failed capture, if any
         self.graph_f = self.graph_b = None
         self.key = None                        # (shape, dtype) of the captured input
         self.static_x = self.static_y = self.static_gy = None
@@ -78,6 +84,16 @@ class GraphedForwardBackward:
         self._anchor = torch.zeros((), device=ddp.device, requires_grad=True)    # makes autograd record the node
         self._mods = list(ddp.module.modules())
         self._mode_sig = None
+        # The capture stream, and every parameter's AccumulateGrad node created (and kept alive) under it.  Autograd caches
+        # that node per parameter for as long as any graph references it and binds it to the stream that was current when it
+        # was made; at the end of a backward the engine orders the caller's stream after every such "leaf stream".  A node
+        # left over from an eager step on the caller's stream (the caller still holds that step's loss) would make the
+        # captured backward wait for uncaptured work -- an invalid capture.  Pinned here, the nodes belong to the capture
+        # stream for good: inside the capture there is nothing to wait for, outside it the engine's ordinary cross-stream
+        # ordering applies.
+        self.stream = torch.cuda.Stream(device=ddp.device)
+        with torch.enable_grad(), torch.cuda.stream(self.stream):
+            self._accumulators = [p.view_as(p).grad_fn.next_functions[0][0] for p in ddp.params]
 
     # ------------------------------------------------------------------ dispatch
     def _modes(self):
@@ -86,7 +102,7 @@ class GraphedForwardBackward:
     def wants(self, args, kwargs) -> bool:
         """True when this call can be served by (capturing or replaying) the graphs."""
         d = self.ddp
-        if not (self.enabled and d.training and torch.is_grad_enabled() and d.require_backward_grad_sync):
+        if not (self.enabled and not self.paused and d.training and torch.is_grad_enabled() and d.require_backward_grad_sync):
             return False
         if kwargs or len(args) != 1 or not torch.is_tensor(args[0]):
             return False
@@ -99,9 +115,11 @@ class GraphedForwardBackward:
 
     def __call__(self, x: torch.Tensor) -> torch.Tensor:
         if self.graph_f is None:
+            ambient = torch.cuda.current_stream(self.ddp.device)
             try:
                 self._capture(x)
             except Exception as exc:          # fall back for good: the eager path is always correct
+                torch.cuda.set_stream(ambient)        # torch.cuda.graph does not restore it when ending the capture raises
                 self._abandon(exc)
                 return self.ddp._forward_eager(x)
         self.replays += 1
@@ -123,24 +141,26 @@ class GraphedForwardBackward:
         snap = [t.clone() for t in state]
         self._undo = (state, snap)
         # warm-up outside the capture: lazily created buffers, function attributes, tensor maps, the reducer's first pass
-        s = torch.cuda.Stream(device=dev)
+        s = self.stream
         s.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(s):
             for _ in range(self.warmup_iters):
                 y = d._forward_eager(self.static_x)
+                if not torch.is_tensor(y) or not y.requires_grad:
+                    raise _NotCapturable("the module must return one tensor that requires grad")
                 gy = torch.zeros_like(y)
-                y.backward(gy)
+                self._backward(y, gy)
         del y
         torch.cuda.current_stream(dev).wait_stream(s)
         torch.cuda.synchronize(dev)
         self.static_gy = gy
         gf, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
         n0 = L.LAUNCHES[0]
-        with torch.cuda.graph(gf):
+        with torch.cuda.graph(gf, stream=s):
             y = d._forward_eager(self.static_x)
         n1 = L.LAUNCHES[0]
-        with torch.cuda.graph(gb, pool=gf.pool()):
-            y.backward(self.static_gy)
+        with torch.cuda.graph(gb, pool=gf.pool(), stream=s):
+            self._backward(y, self.static_gy)
         n2 = L.LAUNCHES[0]
         self.static_y = y.detach()
         del y
@@ -158,9 +178,23 @@ class GraphedForwardBackward:
         log.debug("b200ddp: forward/backward captured for input %s (%d + %d kernels per replay)", self.key,
                   self.launches_f, self.launches_b)
 
+    def _backward(self, y, gy):
+        """Backward of the captured region: ``torch.autograd.grad`` with the parameters as explicit inputs, so that what
+        autograd itself would add to a ``param.grad`` comes back here instead.  Every native layer deposits its weight
+        gradient straight in the arena and reports ``None``; a parameter that does come back with a gradient belongs to a
+        layer this mode cannot serve (its accumulation would have to be replayed too) -- found during the eager warm-up,
+        before anything is captured."""
+        grads = torch.autograd.grad((y,), self.ddp.params, (gy,), allow_unused=True)
+        if any(g is not None for g in grads):
+            names = [str(tuple(p.shape)) for p, g in zip(self.ddp.params, grads) if g is not None][:4]
+            raise _NotCapturable("parameters %s receive their gradient through autograd, not through the arena sinks of the "
+                                 "native layers" % ", ".join(names))
+
     def _abandon(self, exc):
+        import traceback
         d = self.ddp
         self.enabled = False
+        self.failure = "".join(traceback.format_exception(type(exc), exc, exc.__traceback__))
         STATS["capture_failures"] += 1
         self.graph_f = self.graph_b = None
         self.static_y = self.static_gy = None
@@ -177,6 +211,14 @@ class GraphedForwardBackward:
         except Exception:
             pass
         self._undo = None
+        if not isinstance(exc, _NotCapturable):
+            # a capture that died half-way can leave the device's default generator marked "capturing" (the next
+            # torch.randn(device=...) would raise): swap in a copy of its state, which starts out not capturing
+            try:
+                gen = torch.cuda.default_generators[d.device.index if d.device.index is not None else torch.cuda.current_device()]
+                gen.graphsafe_set_state(gen.clone_state())
+            except Exception:
+                pass
         log.warning("b200ddp: forward/backward graph capture failed (%s: %s); this module runs eagerly",
                     type(exc).__name__, str(exc).splitlines()[0][:200] if str(exc) else "")
 

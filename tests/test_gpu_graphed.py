@@ -53,7 +53,7 @@ def test_graphed_forward_backward_trains_like_eager(model_name, dtype):
             # moves the weights, so a graph that kept reading anything stale would show at the next step
             res = {}
             for mode in ("eager", "graph"):
-                g.enabled = mode == "graph"
+                g.paused = mode == "eager"
                 opt.zero_grad()                   # set_to_none=True: every param.grad is dropped, as in the script
                 out = ddp(x)
                 loss = crit(out, y)
@@ -69,6 +69,8 @@ def test_graphed_forward_backward_trains_like_eager(model_name, dtype):
             opt.step()                            # on the graph path's gradients
         torch.cuda.synchronize()
         st = {k: graphed.STATS[k] - before[k] for k in before}
+        if g.failure:
+            print("CAPTURE FAILURE\n" + g.failure)
         assert st["captures"] == 1 and st["capture_failures"] == 0, st
         assert st["forward_replays"] == steps and st["backward_replays"] == steps and st["eager_forwards"] == steps, st
         print(model_name, dtype, "worst relative gradient difference graph vs eager %.2e" % worst, st)
@@ -99,6 +101,38 @@ def test_graphed_forward_backward_trains_like_eager(model_name, dtype):
         torch.cuda.synchronize()
     finally:
         nv.SPLIT_K[0], bmod._FUSE_BN_STATS[0] = saved
+        bd.set_compute_dtype("bf16")
+        if not started:
+            bd.destroy_process_group()
+
+
+def test_module_with_a_stock_layer_falls_back_cleanly():
+    """A parameter whose gradient comes through autograd (a stock ``nn.Linear``) cannot be served by the replayed backward:
+    the warm-up notices, nothing is captured, the loop trains launch by launch and the device's RNG is untouched."""
+    bd, started = _setup()
+    from b200ddp.runtime import graphed
+    dev = bd.get_device()
+    bd.set_compute_dtype("fp32")
+    try:
+        torch.manual_seed(3)
+        net = nn.Sequential(nn.Flatten(), nn.Linear(3 * 32 * 32, 10)).to(dev)
+        ref = nn.Sequential(nn.Flatten(), nn.Linear(3 * 32 * 32, 10)).to(dev)
+        ref.load_state_dict(net.state_dict())
+        ddp = bd.DistributedDataParallel(net, graph_forward_backward=True)
+        before = dict(graphed.STATS)
+        opt, opt_r = torch.optim.SGD(ddp.parameters(), lr=0.1), torch.optim.SGD(ref.parameters(), lr=0.1)
+        for _ in range(3):
+            x, y = torch.randn(16, 3, 32, 32, device=dev), torch.randint(0, 10, (16,), device=dev)
+            for m, o in ((ddp, opt), (ref, opt_r)):
+                o.zero_grad()
+                nn.functional.cross_entropy(m(x), y).backward()
+                o.step()
+        st = {k: graphed.STATS[k] - before[k] for k in before}
+        assert st["captures"] == 0 and st["capture_failures"] == 1 and st["forward_replays"] == 0, st
+        assert not ddp._graphed.enabled
+        for a, b in zip(ddp.module.parameters(), ref.parameters()):
+            assert torch.allclose(a, b, rtol=1e-5, atol=1e-6)
+    finally:
         bd.set_compute_dtype("bf16")
         if not started:
             bd.destroy_process_group()
