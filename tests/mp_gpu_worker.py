@@ -1,6 +1,6 @@
 """Multi-GPU worker (one process per GPU, run under torch.distributed.run by tests/test_gpu_multi.py or by hand):
 
-    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port P tests/mp_gpu_worker.py collectives|ddp|skip
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port P tests/mp_gpu_worker.py collectives|ddp|graphed|skip
 
 Every check prints ``CHECK <name> ok|FAIL <detail>`` on rank 0; the last line is ``MP_GPU_RESULT <json>``.
 
@@ -12,6 +12,9 @@ Every check prints ``CHECK <name> ok|FAIL <detail>`` on rank 0; the last line is
   ddp          DDP semantics on NVLink: wrap-time broadcast, synced grads == mean(local grads) and bitwise equal across
                ranks (workshop Net and resnet18, fp32 mode), no_sync keeps gradients local, BN buffers follow rank 0,
                parameters stay identical through captured training steps.
+  graphed      the caller-owned loop on DistributedDataParallel(graph_forward_backward=True): collectives inside the two replayed
+               graphs (synced grads == mean(local), parameters identical after training); SGD.sync_state() after steps with
+               the optimizer inside the collectives.
   skip         fail-fast: rank 1 skips a collective -> the other ranks' device-side spin times out and
                ``check_health()`` raises (reference behaviour: the launcher aborts the job, nb2:284).
 """
@@ -219,6 +222,56 @@ def graphed():
             check("resnet18 graphed: BN buffers follow rank 0", all(torch.allclose(bufs[0], b, rtol=1e-5, atol=1e-6) for b in bufs[1:]))
         del opt, model
     bd.get_comm().check_health()
+    fused_momentum()
+
+
+def fused_momentum():
+    """``SGD.sync_state()``: with the optimizer folded into the bucket collectives a rank only ever updates the momentum of the
+    shards it owns; before a resume checkpoint the buffers are completed (sum over ranks of the owned shards).  Checked
+    against the same four steps with the optimizer as a separate pass, where every rank holds the whole state."""
+    from b200ddp.models import get_model
+    from b200ddp.nn import CrossEntropyLoss
+    from b200ddp.ops import optim as boptim
+    from b200ddp.runtime.engine import TrainStep
+    rank, dev = bd.get_rank(), bd.get_device()
+    bd.set_compute_dtype("fp32")
+    B = 32
+    g = torch.Generator().manual_seed(7 + rank)
+    xs = torch.randint(0, 256, (B, 32, 32, 3), dtype=torch.uint8, generator=g).pin_memory()
+    ys = torch.randint(0, 10, (B,), generator=g).pin_memory()
+    out = {}
+    saved = os.environ.get("B200DDP_FUSED_SGD")
+    try:
+        for fused in (True, False):
+            os.environ["B200DDP_FUSED_SGD"] = "1" if fused else "0"
+            torch.manual_seed(99)
+            model = bd.DistributedDataParallel(get_model("custom").to(dev))
+            opt = boptim.SGD(model.parameters(), lr=0.01, momentum=0.9)
+            step = TrainStep(model, CrossEntropyLoss(), opt, B, device=dev, graph=True, augment=False)
+            for _ in range(4):
+                step(xs, ys)
+            torch.cuda.synchronize()
+            mom = list(opt._momentum_flat.values())[0]
+            if fused:
+                check("fused SGD: the optimizer runs inside the collectives", bool(step.fused_optimizer))
+                part = gather_cpu(mom)
+                check("fused SGD: a rank holds only its own shards' momentum", not torch.equal(part[0], part[1]))
+                opt.sync_state()
+                opt.sync_state()                 # a second call must not add the shards again
+                torch.cuda.synchronize()
+            out[fused] = (gather_cpu(mom), model.flat_params.detach().cpu())
+            del step, opt, model
+    finally:
+        if saved is None:
+            os.environ.pop("B200DDP_FUSED_SGD", None)
+        else:
+            os.environ["B200DDP_FUSED_SGD"] = saved
+    mf, mu = out[True][0], out[False][0]
+    check("sync_state: momentum identical on every rank", all(torch.equal(mf[0], t) for t in mf[1:]))
+    rel = float((mf[0] - mu[0]).norm() / (mu[0].norm() + 1e-30))
+    check("sync_state: momentum == the separate optimizer pass's", rel < 1e-4, "rel %.2e" % rel)
+    relp = float((out[True][1] - out[False][1]).norm() / (out[False][1].norm() + 1e-30))
+    check("fused SGD: parameters == the separate optimizer pass's", relp < 1e-5, "rel %.2e" % relp)
 
 
 def skip():

@@ -56,7 +56,7 @@ def test_graphed_forward_backward_on_nvlink(world):
     if world not in _worlds():
         pytest.skip("needs %d GPUs" % world)
     v = _run("graphed", world, 29670 + world)
-    assert v["checks"] >= 12
+    assert v["checks"] >= 17
 
 
 def test_rank_that_skips_a_collective_is_detected():
