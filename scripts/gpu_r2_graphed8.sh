@@ -8,5 +8,5 @@ for n in 8 4; do
 import json,sys
 d=json.loads(sys.stdin.read()); print('  N=$n value %.0f ms %.3f launches %s %s' % (d.get('value',0), d.get('ms_per_step',0), d.get('gpu_launches'), d.get('config',{}).get('graphed_forward_backward')))" 2>&1 | cut -c1-400
 done
-timeout 300 python -m pytest "tests/test_gpu_multi.py::test_graphed_forward_backward_on_nvlink[8]" -q -p no:cacheprovider -s > gpurun_out/r2m_tests.log 2>&1; echo "tests rc=$?" | tee -a gpurun_out/r2m_rc.txt
-grep -E "passed|failed" gpurun_out/r2m_tests.log | tail -n 2; grep -E "^CHECK" gpurun_out/r2m_tests.log | cut -c1-200; grep -E "^E  " gpurun_out/r2m_tests.log | head -n 20 | cut -c1-400
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29711 tests/mp_gpu_worker.py graphed > gpurun_out/r2m_graphed_world8.log 2>&1; echo "graphed worker world 8 rc=$?" | tee -a gpurun_out/r2m_rc.txt
+grep -E "^CHECK|^MP_GPU_RESULT" gpurun_out/r2m_graphed_world8.log | cut -c1-220; grep -E "Error|error" gpurun_out/r2m_graphed_world8.log | head -n 10 | cut -c1-300
