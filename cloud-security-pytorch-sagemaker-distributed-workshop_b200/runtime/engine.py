@@ -37,6 +37,9 @@ class TrainStep:
         self.steps_done = 0
         self._graph = None
         self._captured_batch = None
+        self._captured_key = None           # optimizer hyper-parameters the captured launches carry as kernel arguments
+        self._recaptures = 0
+        self._recapture_run = (0, -2)       # (length of the current run of consecutive re-captures, step of the last one)
         import os
         from ..models.workshop_net import WorkshopNet
         core = model.module if hasattr(model, "module") else model
@@ -143,6 +146,35 @@ class TrainStep:
             ts.extend(t for t in st.values() if torch.is_tensor(t))
         return ts
 
+    def _hyper_key(self):
+        """The optimizer's scalar hyper-parameters.  In a captured step they are kernel ARGUMENTS (of the optimizer pass and
+        of the fused bucket step alike), so a replay keeps the values of capture time: a learning-rate schedule has to be
+        noticed on the host."""
+        return tuple(tuple((k, v) for k, v in sorted(g.items()) if k != "params" and isinstance(v, (bool, int, float, tuple)))
+                     for g in self.optimizer.param_groups)
+
+    def _stale(self) -> bool:
+        return self._graph is not None and self._hyper_key() != self._captured_key
+
+    def _recapture(self):
+        """A hyper-parameter changed (``param_groups[0]['lr'] = ...``, an LR scheduler): capture the step again with the new
+        values.  Costs a warm-up + capture (~0.1 s), fine for a per-epoch schedule; a schedule that moves EVERY step would
+        pay that on every step, so after four re-captures in a row the engine runs launch by launch instead, where the
+        optimizer reads its hyper-parameters at every step."""
+        run, last = self._recapture_run
+        run = run + 1 if self.steps_done - last <= 1 else 1
+        self._recapture_run = (run, self.steps_done)
+        self._recaptures += 1
+        torch.cuda.synchronize(self.device)
+        self._graph = None
+        if run > 4:
+            import warnings
+            warnings.warn("b200ddp.TrainStep: optimizer hyper-parameters change at every step; the step now runs without a "
+                          "CUDA graph (keep them in place for several steps, or pass graph=False)")
+            self.use_graph = False
+            return
+        self._capture()
+
     def _capture(self):
         # The warm-up iterations are real optimizer steps on whatever batch sits in the static inputs; they exist to run the
         # one-time set-up (function attributes, lazily created buffers, optimizer state) outside the capture.  The training
@@ -168,6 +200,7 @@ class TrainStep:
             loss = self._body(self.static_x, self.static_y, self.static_off)
             self.static_loss.copy_(loss)
         self._graph = g
+        self._captured_key = self._hyper_key()
         self._pipe_init()
         with torch.no_grad():
             for t, c in zip(before, snap):
@@ -192,6 +225,10 @@ class TrainStep:
                 self.static_x.copy_(x_u8, non_blocking=True)
                 self.static_y.copy_(y, non_blocking=True)
                 self._capture()
+            elif self._stale():
+                self._recapture()
+                if self._graph is None:                  # the engine gave up on graphs (see _recapture)
+                    return self(x_u8, y, need_loss=need_loss)
             self.static_x.copy_(x_u8, non_blocking=True)
             self.static_y.copy_(y, non_blocking=True)
             if offsets is not None:
@@ -237,7 +274,7 @@ class TrainStep:
         pending = None                       # slot whose loss has not been yielded yet
         k = 0
         for x, y in batches:
-            if x.shape[0] != self.batch_size or self._graph is None:
+            if x.shape[0] != self.batch_size or self._graph is None or self._stale():
                 if pending is not None:
                     P["ready"][pending].synchronize()
                     yield float(P["pin_loss"][pending].item()) if need_loss else None
