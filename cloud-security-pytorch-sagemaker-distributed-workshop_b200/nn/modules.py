@@ -129,13 +129,20 @@ class Linear(nn.Linear):
         return BF.linear(x, self.weight, self.bias, self.fused_relu, nh)
 
 
-# When set, BatchNorm2d does not launch one `num_batches_tracked += 1` kernel per layer per step; the
-# trainer adds the step count once before a checkpoint is written (`flush_bn_counters`).
+# Deferred counters: BatchNorm2d does not launch one `num_batches_tracked += 1` kernel per layer per step; whoever owns the
+# step adds the step count once before a checkpoint is written (`flush_bn_counters`).  Scoped to the BatchNorm layers of ONE
+# model (`defer_bn_counters(True, model)`, what `TrainStep` does): another model in the same process keeps counting by
+# itself.  Without a model the switch is process-wide (profiling scripts).
 _DEFER_BN_COUNTER = [False]
 
 
-def defer_bn_counters(flag: bool = True) -> None:
-    _DEFER_BN_COUNTER[0] = bool(flag)
+def defer_bn_counters(flag: bool = True, model: Optional[nn.Module] = None) -> None:
+    if model is None:
+        _DEFER_BN_COUNTER[0] = bool(flag)
+        return
+    for m in model.modules():
+        if isinstance(m, nn.BatchNorm2d):
+            m._b200_defer_counter = bool(flag)
 
 
 def flush_bn_counters(model: nn.Module, steps: int) -> None:
@@ -161,7 +168,7 @@ class BatchNorm2d(nn.BatchNorm2d):
             if residual is not None:
                 residual = BF.as_activation(residual)
             if (self.training and self.track_running_stats and self.num_batches_tracked is not None
-                    and not _DEFER_BN_COUNTER[0]):
+                    and not (_DEFER_BN_COUNTER[0] or getattr(self, "_b200_defer_counter", False))):
                 self.num_batches_tracked.add_(1)
         return BF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, training,
                              self.momentum if self.momentum is not None else 0.1, self.eps, self.fused_relu, residual,

@@ -65,8 +65,7 @@ class TrainStep:
             self.pin_loss = torch.zeros((), dtype=torch.float32).pin_memory()
             from ..parallel import process_group as _pg
             self._comm = _pg.get_comm()         # polled after every step: a timed-out collective must not go unnoticed
-            BF.assume_unit_loss_grad(True)
-            bmod.defer_bn_counters(True)
+            bmod.defer_bn_counters(True, model)      # this model's layers only; flush_counters() adds the steps back
             # Off by default: measured on one B200 (resnet18, fp32) the pooled form saves 15 launches per step and is SLOWER,
             # 1.370 vs 1.270 ms at batch 256 and 0.793 vs 0.766 ms at batch 32 -- every CTA of the apply kernel then derives
             # 8 scale/shift pairs from the sums (32 dependent loads + rsqrt) before it touches its first row, while the tiny
@@ -99,6 +98,16 @@ class TrainStep:
         pinned_np[:, 2] = self.rng.randint(0, 2, n)
 
     def _body(self, x_u8, y, offsets):
+        # this engine calls backward() on the raw loss: the fused criterion may skip its gradient-scale kernel -- for the
+        # duration of this step only (a process-wide switch would silently drop another caller's `(loss * w).backward()`)
+        prev = BF._unit_loss_grad[0]
+        BF._unit_loss_grad[0] = self.cuda
+        try:
+            return self._body_impl(x_u8, y, offsets)
+        finally:
+            BF._unit_loss_grad[0] = prev
+
+    def _body_impl(self, x_u8, y, offsets):
         from ..ops import native as nv
         if self.cuda and self._net_mega is not None:
             # workshop Net: augmentation + forward/loss/backward megakernel (2 launches) + fused SGD
@@ -362,7 +371,11 @@ class TrainStep:
                 self.optimizer.zero_grad()
                 loss = self.criterion(self.model(inp), yd)
             ev["t1"].record()
-            loss.backward(self._one)
+            prev, BF._unit_loss_grad[0] = BF._unit_loss_grad[0], True
+            try:
+                loss.backward(self._one)
+            finally:
+                BF._unit_loss_grad[0] = prev
             ev["t2"].record()
             self.optimizer.step()
             ev["t3"].record()
