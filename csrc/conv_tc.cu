@@ -487,6 +487,10 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
     } else {
       // ---- cluster split-K: the ZC CTAs of a cluster hold partial sums of the same tile.  Stage the
       // partial in shared memory (column-major: conflict-free, one row per thread) ...
+      // (Measured alternative, rejected: row-major staging with 16-byte stores and 16-byte ld.shared::cluster reads, rows
+      // BN + 4 floats apart -- a quarter of the load instructions, but every lane of a remote load then touches its own
+      // 128-byte line: the join went from 2.4 to 5.2 us per kernel and the resnet18 step from 1.27 to 1.47 ms.  Remote
+      // shared memory wants the lanes of one load on consecutive words, like global memory.)
       float* stage = reinterpret_cast<float*>(smem);        // the operand ring is idle now: all MMAs retired
 #pragma unroll 1
       for (int cb = 0; cb < BN / 32; ++cb) {
@@ -523,6 +527,7 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
     }
   }
   STAMP(4, 0);         // epilogue phase 1 done (direct store, or partial staged)
+  static_assert(ZC == 1 || (size_t)BM * BN * 4 <= (size_t)ST * C::STAGE_BYTES, "split-K staging must fit the operand ring");
   if (ZC > 1) {
     // ... then every CTA reduces its BN/ZC column slice over all peers through distributed shared memory
     // (ld.shared::cluster) and runs the epilogue for that slice.  No atomics, no global scratch.
@@ -543,7 +548,9 @@ conv_tc_kernel(const __grid_constant__ ConvParams p, const __grid_constant__ CUt
 #pragma unroll
         for (int q = 0; q < SLICE; ++q) f[q] += ld_dsmem_f32(base + (uint32_t)q * BM * 4u);
       }
+      STAMP(8, 0);     // peers' partial sums read
       if (MODE == MODE_FWD && p.bn_sums != nullptr) bn_stats_accumulate<SLICE>(p, n0 + rank * SLICE, f, lane);
+      STAMP(9, 0);
       if (MODE != MODE_WGRAD || p.nvk > 0) epilogue_store<T, MODE, SLICE>(p, m, n0 + rank * SLICE, f);
     }
     STAMP(6, 0);
@@ -719,10 +726,36 @@ uint32_t cluster_cap() {
   }
   return cap;
 }
-uint32_t cluster_split(uint32_t want) {
+// ... but with only a handful of tiles there is nothing to strand: up to B200DDP_CLUSTER8_TILES tiles (default 8) split 8 ways.
+// Measured on the fp32 resnet18 step, one B200 (profiles/r2/conv_tile_tuning.md): batch 32, 0.700 -> 0.658 ms; batch 256 unchanged.
+uint32_t cluster8_tiles() {
+  static int thr = -1;
+  if (thr < 0) {
+    const char* e = getenv("B200DDP_CLUSTER8_TILES");
+    thr = e ? atoi(e) : 8;
+    if (thr < 0) thr = 0;
+  }
+  return (uint32_t)thr;
+}
+uint32_t cluster_split(uint32_t want, uint32_t tiles = 0xffffffffu) {
+  const uint32_t cap = tiles <= cluster8_tiles() ? 8u : cluster_cap();
   uint32_t zc = 1;
-  while (zc * 2 <= want && zc * 2 <= cluster_cap()) zc *= 2;
+  while (zc * 2 <= want && zc * 2 <= cap) zc *= 2;
   return zc;
+}
+
+// FWD/DGRAD with few 128-wide tiles: 64-wide tiles instead -- twice the CTAs streaming operands, half the columns per CTA to
+// stage and to pull from the cluster peers in the split-K join.  `tiles128` = tile count with BN = 128; the threshold comes
+// from B200DDP_NARROW_TILES (default 18; 0 = only when Cout <= 64).  Measured on the fp32 resnet18 step, one B200: batch 32,
+// 0.766 -> 0.700 ms; batch 256, 1.273 -> 1.262 ms; thresholds of 40 and 150 change nothing further.
+bool prefer_narrow(uint32_t tiles128) {
+  static int thr = -1;
+  if (thr < 0) {
+    const char* e = getenv("B200DDP_NARROW_TILES");
+    thr = e ? atoi(e) : 18;
+    if (thr < 0) thr = 0;
+  }
+  return thr > 0 && tiles128 <= (uint32_t)thr;
 }
 
 // FWD/DGRAD: split K over a cluster when the tile grid alone cannot fill the machine
@@ -732,15 +765,15 @@ uint32_t plan_cluster(ConvParams& p, uint32_t tiles) {
   if (!g_split_k || tiles * 2 > sms || p.nvk < 4) return 1;
   uint32_t want = sms / tiles;
   if (want > p.nvk / 2) want = p.nvk / 2;            // >= 2 k-blocks per CTA
-  const uint32_t zc = cluster_split(want);
+  const uint32_t zc = cluster_split(want, tiles);
   p.kb_per_split = (p.nvk + zc - 1) / zc;
   return zc;
 }
 
 }  // namespace
 
-extern "C" int b200_conv_set_profile_buffer(long long* dev_buf8) {
-  g_prof = dev_buf8;
+extern "C" int b200_conv_set_profile_buffer(long long* dev_buf16) {   // 16 slots (8 phase boundaries + 2 inside the split-K join)
+  g_prof = dev_buf16;
   return 0;
 }
 
@@ -760,7 +793,7 @@ static int conv_fwd_impl(const void* x, const void* w, const float* bias, void* 
   p.x = x; p.w = w; p.out = y; p.bias = bias; p.relu = relu; p.bn_sums = bn_sums;
   p.gemm_m = (uint32_t)p.N * p.Ho * p.Wo; p.gemm_n = p.Kc; p.gemm_k = (uint32_t)p.R * p.S * p.C;
   plan_k(p, p.C, El<T>::BK);
-  const bool narrow = p.gemm_n <= 64;
+  const bool narrow = p.gemm_n <= 64 || prefer_narrow(((p.gemm_m + BM - 1) / BM) * ((p.gemm_n + 127) / 128));
   const uint32_t bn = narrow ? 64 : 128;
   dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, 1);
   const uint32_t zc = plan_cluster(p, grid.x * grid.y);
@@ -809,7 +842,7 @@ static int conv_dgrad_impl(const void* dy, const void* w, void* dx, const b200_c
   p.dy = dy; p.w = w; p.out = dx; p.residual = residual;
   p.gemm_m = (uint32_t)p.N * p.H * p.W; p.gemm_n = p.C; p.gemm_k = (uint32_t)p.R * p.S * p.Kc;
   plan_k(p, p.Kc, El<T>::BK);
-  const bool narrow = p.gemm_n <= 64;
+  const bool narrow = p.gemm_n <= 64 || prefer_narrow(((p.gemm_m + BM - 1) / BM) * ((p.gemm_n + 127) / 128));
   const uint32_t bn = narrow ? 64 : 128;
   dim3 grid((p.gemm_m + BM - 1) / BM, (p.gemm_n + bn - 1) / bn, 1);
   const uint32_t zc = plan_cluster(p, grid.x * grid.y);

@@ -235,7 +235,7 @@ typedef struct b200_conv_geom {
  * pins fwd/dgrad to one CTA per tile. */
 int b200_conv_set_split_k(int enabled);
 /* Tuning aid: when non-NULL, CTA (0,0,0) of every conv launch writes 8 clock64() phase stamps there. */
-int b200_conv_set_profile_buffer(long long* dev_buf8);
+int b200_conv_set_profile_buffer(long long* dev_buf16);   /* 16 clock64 slots, tuning aid */
 int b200_conv_fwd(const void* x, const void* w, const float* bias, void* y, const b200_conv_geom* g, int relu,
                   void* stream);
 /* the same convolution without bias/ReLU whose epilogue also accumulates per-channel sum / sum of squares of the output

@@ -10,3 +10,7 @@ import json,sys
 d=json.loads(sys.stdin.read()); c=d['config']; l=c.get('like_for_like') or {}
 print('value %.0f e2e %.0f ms %.4f dtype %s launches %s clocks %s' % (d['value'], d['e2e']['value'], d['ms_per_step'], d['dtype'], d.get('gpu_launches'), d.get('clocks')))
 print('ratios', l.get('ratio_product_over_torch')); print('secondary', c.get('secondary'))" 2>&1 | cut -c1-900
+timeout 200 python bench.py --steps 100 --warmup 5 --no-like-for-like --no-secondary --global-batch 32 > gpurun_out/r2z_bench_b32.log 2>&1; echo "bench b32 rc=$?" | tee -a gpurun_out/r2z_rc.txt
+grep '^{' gpurun_out/r2z_bench_b32.log | tail -n 1 | python -c "
+import json,sys
+d=json.loads(sys.stdin.read()); print('batch 32 (what each rank of an 8-GPU job runs): %.4f ms  %.0f img/s' % (d['ms_per_step'], d['value']))" 2>&1 | cut -c1-200
