@@ -10,8 +10,8 @@ between ``model(data)`` and the gradients: ~60 Python autograd functions and ~13
 the eager path cost 5-9 ms of host time for 0.8-1.3 ms of GPU work.  ``GraphedForwardBackward`` captures
 
     graph F:  [BN-buffer broadcast]  y = module(x)                                      (autograd recording)
-    graph B:  y.backward(gy)  -> dgrad chain, wgrads on the auxiliary stream straight into the gradient arena, the bucket
-              collectives on the comm stream, the join
+    graph B:  the backward from gy -> dgrad chain, wgrads on the auxiliary stream straight into the gradient arena, the
+              bucket collectives on the comm stream, the join
 
 from static input / output / output-gradient buffers in one private memory pool, and ``model(data)`` becomes: copy ``data`` in,
 replay F, return ``y``; ``loss.backward()`` reaches the node's backward: copy ``gy`` in, replay B.  ``param.grad`` are the
@@ -19,8 +19,14 @@ arena views the graph writes, so any optimizer (the script's ``torch.optim.SGD``
 
 Everything that does not fit the captured shape runs eagerly, as before: evaluation / ``no_grad``, another batch size (the
 last short batch of an epoch), ``no_sync()``, keyword arguments, a changed train/eval pattern of the sub-modules, a caller
-that is itself capturing.  One output may be back-propagated once, and only until the next training forward (the activations
-the backward needs live in the graph's pool and are overwritten by the next replay) -- a stale backward raises.
+that is itself capturing, a module with a layer whose parameter gradients come through autograd instead of the arena sinks
+(noticed in the eager warm-up, before anything is captured).  One output may be back-propagated once, and only until the next
+training forward (the activations the backward needs live in the graph's pool and are overwritten by the next replay) -- a
+stale backward raises.
+
+Measured with the reference's unmodified GPU script on this framework (``bench.py --impl reference_on_b200``, the script's own
+PIL loader in the timed region): 8.9k / 17.3k / 31.1k / 53.4k img/s at 1 / 2 / 4 / 8 GPUs against 7.0k / 11.3k / 16.4k / 18.2k
+with every launch eager and 7.6k / 12.1k / 18.0k / 25.3k for the reference itself (``BASELINE.md``).
 """
 from __future__ import annotations
 
