@@ -167,9 +167,9 @@ class BatchNorm2d(nn.BatchNorm2d):
             x = BF.as_activation(x)
             if residual is not None:
                 residual = BF.as_activation(residual)
-            if (self.training and self.track_running_stats and self.num_batches_tracked is not None
-                    and not (_DEFER_BN_COUNTER[0] or getattr(self, "_b200_defer_counter", False))):
-                self.num_batches_tracked.add_(1)
+        if (self.training and self.track_running_stats and self.num_batches_tracked is not None
+                and not (_DEFER_BN_COUNTER[0] or getattr(self, "_b200_defer_counter", False))):
+            self.num_batches_tracked.add_(1)          # CPU fallback included: state_dict parity with nn.BatchNorm2d
         return BF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, training,
                              self.momentum if self.momentum is not None else 0.1, self.eps, self.fused_relu, residual,
                              presummed)

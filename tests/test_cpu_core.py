@@ -307,3 +307,30 @@ def test_sgd_sync_state_shard_ownership_matches_the_fused_kernel():
                 lo, hi = min(rank * per, chunks) * 4, min((rank + 1) * per, chunks) * 4
                 assert float(m[b.start + lo: b.start + hi].sum()) == hi - lo
         assert torch.equal(total, torch.ones(144)), world
+
+
+def test_resnet18_cpu_fallback_matches_torchvision_including_bn_bookkeeping():
+    """The CPU fallback of the native layers is plain torch math: one training step of resnet18 must leave the same outputs,
+    running statistics and ``num_batches_tracked`` as torchvision's model with the same weights (``state_dict`` parity)."""
+    import torchvision
+    from b200ddp.models import get_model
+    torch.manual_seed(0)
+    ours = get_model("resnet18")
+    ref = torchvision.models.resnet18()
+    ref.load_state_dict(ours.state_dict())
+    ours.train()
+    ref.train()
+    x = torch.randn(4, 3, 32, 32)
+    yo, yr = ours(x), ref(x)
+    assert torch.allclose(yo, yr, rtol=1e-4, atol=1e-4)
+    so, sr = ours.state_dict(), ref.state_dict()
+    assert set(so) == set(sr)
+    for k in sr:
+        if k.endswith("num_batches_tracked"):
+            assert int(so[k]) == int(sr[k]) == 1, k
+        elif "running_" in k:
+            assert torch.allclose(so[k], sr[k], rtol=1e-4, atol=1e-5), k
+    yo.sum().backward()
+    yr.sum().backward()
+    for (n, a), (_, b) in zip(ours.named_parameters(), ref.named_parameters()):
+        assert torch.allclose(a.grad, b.grad, rtol=2e-3, atol=2e-4), n
