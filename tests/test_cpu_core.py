@@ -334,3 +334,45 @@ def test_resnet18_cpu_fallback_matches_torchvision_including_bn_bookkeeping():
     yr.sum().backward()
     for (n, a), (_, b) in zip(ours.named_parameters(), ref.named_parameters()):
         assert torch.allclose(a.grad, b.grad, rtol=2e-3, atol=2e-4), n
+
+
+def test_train_step_notices_hyper_parameter_changes_and_scopes_its_switches():
+    """Host-side logic of ``TrainStep`` that needs no GPU: a changed learning rate makes a captured step stale (the GPU test
+    ``tests/test_gpu_engine.py`` checks the re-capture itself); deferring the BatchNorm step counters is scoped to the
+    engine's own model; the unit-loss-gradient hint is only on while the engine's step runs."""
+    from b200ddp import nn as bnn
+    from b200ddp.models import get_model
+    from b200ddp.nn import CrossEntropyLoss
+    from b200ddp.ops import functional as BF
+    from b200ddp.ops import optim as boptim
+    from b200ddp.runtime.engine import TrainStep
+    net = get_model("custom")
+    opt = boptim.SGD(net.parameters(), lr=0.1, momentum=0.9)
+    step = TrainStep(net, CrossEntropyLoss(), opt, 4, device=torch.device("cpu"), graph=True)
+    assert not step.use_graph and not step._stale()          # no GPU: nothing is ever captured
+    step._graph, step._captured_key = object(), step._hyper_key()
+    assert not step._stale()
+    opt.param_groups[0]["lr"] = 0.01
+    assert step._stale()
+    step._captured_key = step._hyper_key()
+    opt.param_groups[0]["momentum"] = 0.8
+    assert step._stale()
+    step._graph = None
+    # the step itself still runs (eagerly) and leaves the process-wide hint as it found it
+    BF.assume_unit_loss_grad(False)
+    x = torch.randint(0, 256, (4, 32, 32, 3), dtype=torch.uint8)
+    y = torch.randint(0, 10, (4,))
+    loss = step(x, y, need_loss=True)
+    assert loss == loss and BF._unit_loss_grad[0] is False
+    # counters: deferral set for one model does not silence another model's BatchNorm layers
+    a, b = bnn.BatchNorm2d(8), bnn.BatchNorm2d(8)
+    bnn.defer_bn_counters(True, a)
+    a.train(), b.train()
+    t = torch.randn(2, 8, 4, 4)
+    a(t), b(t)
+    assert int(a.num_batches_tracked) == 0 and int(b.num_batches_tracked) == 1
+    bnn.flush_bn_counters(a, 1)
+    assert int(a.num_batches_tracked) == 1
+    bnn.defer_bn_counters(False, a)
+    a(t)
+    assert int(a.num_batches_tracked) == 2
