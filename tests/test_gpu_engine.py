@@ -31,11 +31,12 @@ def _run(model_name, schedule, graph, init, xs, ys, dev):
 
 # the workshop Net (fp32 megakernel step) is well conditioned: graph and eager runs stay together to rounding, the bound is tight;
 # resnet18 at random initialisation amplifies rounding differences from step to step (profiles/determinism.md), so it gets a gentle
-# schedule and a bound that still separates "followed the schedule" from "kept the captured rate" (which would be off by ~100 %)
+# schedule and a bound that still separates "followed the schedule" (measured: 4 % of the distance moved) from "kept the captured
+# rate" (five more steps at ten to a hundred times the rate: off by more than the distance moved)
 @pytest.mark.parametrize("model_name,name,schedule,recaptures,keeps_graph,bound", [
     ("custom", "per-epoch", [0.1, 0.1, 0.1, 0.01, 0.01, 0.01, 0.001, 0.001], 2, True, 1e-3),
     ("custom", "per-step", [0.1, 0.09, 0.08, 0.07, 0.06, 0.05, 0.04, 0.03], 5, False, 1e-3),
-    ("resnet18", "per-epoch", [0.01, 0.01, 0.01, 0.001, 0.001, 0.001, 0.0001, 0.0001], 2, True, 0.2),
+    ("resnet18", "per-epoch", [0.01, 0.01, 0.01, 0.001, 0.001, 0.001, 0.0001, 0.0001], 2, True, 0.5),
 ])
 def test_learning_rate_schedule_under_graph_replay(model_name, name, schedule, recaptures, keeps_graph, bound):
     import b200ddp as bd
