@@ -1,7 +1,7 @@
-"""Device-side phase timers and clock sampling.
+"""Clock sampling for timed regions.
 
-Every multi-GPU number is a CUDA-event duration reduced with max over ranks
-(``parallel.process_group.max_over_ranks``); nothing here is wall-clock except the nvidia-smi sampler.
+Phase timings themselves are CUDA-event durations reduced with max over ranks (``TrainStep.breakdown``,
+``parallel.process_group.max_over_ranks``); the only wall-clock thing here is the nvidia-smi sampler.
 """
 from __future__ import annotations
 
@@ -9,38 +9,8 @@ import statistics
 import subprocess
 import threading
 import time
-from typing import Dict, List, Optional
+from typing import List, Optional
 
-import torch
-
-
-class CudaTimer:
-    """Accumulates CUDA-event durations per named phase on the current stream."""
-
-    def __init__(self, enabled: bool = True):
-        self.enabled = enabled and torch.cuda.is_available()
-        self._open: Dict[str, torch.cuda.Event] = {}
-        self._pairs: Dict[str, List] = {}
-
-    def start(self, name: str):
-        if not self.enabled:
-            return
-        ev = torch.cuda.Event(enable_timing=True)
-        ev.record()
-        self._open[name] = ev
-
-    def stop(self, name: str):
-        if not self.enabled:
-            return
-        ev = torch.cuda.Event(enable_timing=True)
-        ev.record()
-        self._pairs.setdefault(name, []).append((self._open.pop(name), ev))
-
-    def summary_ms(self) -> Dict[str, float]:
-        if not self.enabled:
-            return {}
-        torch.cuda.synchronize()
-        return {k: sum(a.elapsed_time(b) for a, b in v) for k, v in self._pairs.items()}
 
 
 class ClockSampler:
