@@ -64,6 +64,8 @@ class TrainConfig:
     save_full_checkpoint: bool = False
     max_steps: int = 0                   # 0 = run whole epochs
     trace: str = ""                      # write a Chrome-trace JSON of the training loop here (rank is appended)
+    lr_step_epochs: int = 0              # > 0: multiply the rate by lr_gamma every that many epochs (the reference trains at a constant rate)
+    lr_gamma: float = 0.1
     eval: bool = True
 
     @property
@@ -103,6 +105,8 @@ def add_extension_arguments(parser: argparse.ArgumentParser) -> argparse.Argumen
     parser.add_argument("--max-steps", type=int, default=0)
     parser.add_argument("--no-eval", dest="eval", action="store_false", default=True)
     parser.add_argument("--trace", type=str, default="", help="Chrome-trace JSON of the loop (host + device ranges), per rank")
+    parser.add_argument("--lr-step-epochs", type=int, default=0, help="multiply the learning rate by --lr-gamma every N epochs (0 = constant)")
+    parser.add_argument("--lr-gamma", type=float, default=0.1)
     return parser
 
 

@@ -124,6 +124,12 @@ def train(cfg: TrainConfig):
     t_epoch_img = 0
     for epoch in range(start_epoch, cfg.epochs + 1):
         model.train()
+        if cfg.lr_step_epochs > 0:
+            # step schedule: the captured step carries the rate as a kernel argument, TrainStep re-captures when it moves
+            lr = cfg.lr * cfg.lr_gamma ** ((epoch - 1) // cfg.lr_step_epochs)
+            if optimizer.param_groups[0]["lr"] != lr:
+                optimizer.param_groups[0]["lr"] = lr
+                logger.info("Epoch %d: learning rate %g", epoch, lr)
         t0 = time.time()
         seen_imgs = 0
         # TrainStep.pipeline: batch k+1 is uploaded while step k computes and every loss comes back asynchronously, one

@@ -376,3 +376,25 @@ def test_train_step_notices_hyper_parameter_changes_and_scopes_its_switches():
     bnn.defer_bn_counters(False, a)
     a(t)
     assert int(a.num_batches_tracked) == 2
+
+
+def test_trainer_step_learning_rate_schedule(tmp_path, monkeypatch, capfd):
+    """``--lr-step-epochs / --lr-gamma`` (an extension: the reference trains at a constant rate): the rate the optimizer steps
+    with follows the schedule epoch by epoch, also after a resume."""
+    from b200ddp.utils.config import parse_args
+    from b200ddp.workloads.cifar10_train import train
+    for k in ("SM_HOSTS", "SM_CURRENT_HOST", "RANK", "WORLD_SIZE"):
+        monkeypatch.delenv(k, raising=False)
+    common = ["--model-type", "custom", "--synthetic", "--train-size", "128", "--test-size", "64", "--batch-size", "64", "--test-batch-size", "64",
+              "--lr", "0.1", "--momentum", "0.9", "--backend", "gloo", "--model-dir", str(tmp_path), "--log-interval", "1000", "--no-eval",
+              "--lr-step-epochs", "1", "--lr-gamma", "0.1"]
+    cfg = parse_args(common + ["--epochs", "3", "--save-full-checkpoint"])
+    assert cfg.lr_step_epochs == 1 and cfg.lr_gamma == 0.1
+    capfd.readouterr()
+    train(cfg)
+    out = capfd.readouterr()
+    text = out.out + out.err
+    assert "Epoch 2: learning rate 0.01" in text and "Epoch 3: learning rate 0.001" in text and "Epoch 1: learning rate" not in text
+    train(parse_args(common + ["--epochs", "4", "--resume", str(tmp_path / "checkpoint.pt")]))
+    out = capfd.readouterr()
+    assert "Epoch 4: learning rate 0.0001" in out.out + out.err
