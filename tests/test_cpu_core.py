@@ -378,7 +378,7 @@ def test_train_step_notices_hyper_parameter_changes_and_scopes_its_switches():
     assert int(a.num_batches_tracked) == 2
 
 
-def test_trainer_step_learning_rate_schedule(tmp_path, monkeypatch, capfd):
+def test_trainer_step_learning_rate_schedule(tmp_path, monkeypatch):
     """``--lr-step-epochs / --lr-gamma`` (an extension: the reference trains at a constant rate): the rate the optimizer steps
     with follows the schedule epoch by epoch, also after a resume."""
     from b200ddp.utils.config import parse_args
@@ -390,11 +390,17 @@ def test_trainer_step_learning_rate_schedule(tmp_path, monkeypatch, capfd):
               "--lr-step-epochs", "1", "--lr-gamma", "0.1"]
     cfg = parse_args(common + ["--epochs", "3", "--save-full-checkpoint"])
     assert cfg.lr_step_epochs == 1 and cfg.lr_gamma == 0.1
-    capfd.readouterr()
-    train(cfg)
-    out = capfd.readouterr()
-    text = out.out + out.err
-    assert "Epoch 2: learning rate 0.01" in text and "Epoch 3: learning rate 0.001" in text and "Epoch 1: learning rate" not in text
-    train(parse_args(common + ["--epochs", "4", "--resume", str(tmp_path / "checkpoint.pt")]))
-    out = capfd.readouterr()
-    assert "Epoch 4: learning rate 0.0001" in out.out + out.err
+    import io
+    import logging
+    buf = io.StringIO()
+    handler = logging.StreamHandler(buf)           # the package logger does not propagate: listen to it directly
+    logging.getLogger("b200ddp").addHandler(handler)
+    try:
+        train(cfg)
+        text = buf.getvalue()
+        assert "Epoch 2: learning rate 0.01" in text and "Epoch 3: learning rate 0.001" in text and "Epoch 1: learning rate" not in text
+        buf.truncate(0)
+        train(parse_args(common + ["--epochs", "4", "--resume", str(tmp_path / "checkpoint.pt")]))
+        assert "Epoch 4: learning rate 0.0001" in buf.getvalue()
+    finally:
+        logging.getLogger("b200ddp").removeHandler(handler)
