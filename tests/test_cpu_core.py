@@ -404,3 +404,56 @@ def test_trainer_step_learning_rate_schedule(tmp_path, monkeypatch):
         assert "Epoch 4: learning rate 0.0001" in buf.getvalue()
     finally:
         logging.getLogger("b200ddp").removeHandler(handler)
+
+
+def test_serving_endpoint_ping_and_invocations(tmp_path):
+    """The reference reaches its ``inference.py`` through SageMaker's serving container (nb1:153-211: deploy, then
+    ``predictor.predict``); ``workloads/serve.py`` is that contract stand-alone: ``GET /ping``, ``POST /invocations`` with
+    npy or json bodies, answers equal to calling the hooks directly."""
+    import io
+    import threading
+    import urllib.error
+    import urllib.request
+    from b200ddp.models import get_model
+    from b200ddp.utils.checkpoint import save_model
+    from b200ddp.workloads import inference, serve
+    torch.manual_seed(0)
+    net = get_model("custom")
+    save_model(net, str(tmp_path))
+    srv = serve.make_server(str(tmp_path), port=0)
+    host, port = srv.server_address
+    th = threading.Thread(target=srv.serve_forever, daemon=True)
+    th.start()
+    try:
+        base = "http://%s:%d" % (host, port)
+        with urllib.request.urlopen(base + "/ping", timeout=10) as r:
+            assert r.status == 200 and r.read() == b""
+        x = np.random.RandomState(0).randn(3, 3, 32, 32).astype(np.float32)
+        want = net.eval()(torch.from_numpy(x)).detach().numpy()
+        buf = io.BytesIO()
+        np.save(buf, x)
+        req = urllib.request.Request(base + "/invocations", data=buf.getvalue(), headers={"Content-Type": "application/x-npy",
+                                                                                          "Accept": "application/x-npy"})
+        with urllib.request.urlopen(req, timeout=30) as r:
+            got = np.load(io.BytesIO(r.read()))
+        assert np.allclose(got, want, atol=1e-5)
+        req = urllib.request.Request(base + "/invocations", data=json.dumps(x.tolist()).encode(),
+                                     headers={"Content-Type": "application/json"})
+        with urllib.request.urlopen(req, timeout=30) as r:
+            assert r.headers["Content-Type"] == "application/json"
+            got = np.array(json.loads(r.read()), dtype=np.float32)
+        assert np.allclose(got, want, atol=1e-4)
+        assert np.allclose(got, np.array(json.loads(inference.output_fn(inference.predict_fn(inference.input_fn(buf.getvalue()),
+                                                                                           inference.model_fn(str(tmp_path))))), dtype=np.float32), atol=1e-6)
+        for path, data, headers, code in (("/invocations", b"x", {"Content-Type": "text/csv"}, 415),
+                                          ("/invocations", b"not json", {"Content-Type": "application/json"}, 400),
+                                          ("/nowhere", b"", {}, 404)):
+            try:
+                urllib.request.urlopen(urllib.request.Request(base + path, data=data, headers=headers), timeout=10)
+                raise AssertionError("expected HTTP %d" % code)
+            except urllib.error.HTTPError as e:
+                assert e.code == code, (path, e.code)
+    finally:
+        srv.shutdown()
+        srv.server_close()
+        th.join(timeout=10)
